@@ -1,0 +1,85 @@
+"""ctypes binding of libb2g.so (the C ABI declared in include/b2g.h).
+
+There is NO fallback: if the library is missing, or a call fails, an exception is
+raised.  Tensors cross the boundary as raw device pointers (`tensor.data_ptr()`)
+plus sizes; PyTorch only owns the memory and the stream.
+"""
+import ctypes
+import os
+from ctypes import (POINTER, c_char_p, c_double, c_float, c_int, c_int64, c_uint32,
+                    c_uint64, c_void_p)
+
+import torch
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, 'libb2g.so')
+
+P = c_void_p  # every device pointer / stream
+
+# name -> (restype, argtypes); mirrors include/b2g.h one to one
+SIGNATURES = {
+    'b2g_version': (c_int, []),
+    'b2g_last_error': (c_char_p, []),
+    'b2g_device_sm_count': (c_int, []),
+    'b2g_gae_time_major': (c_int, [P, P, P, P, c_float, c_float, P, P, c_int, c_int64, P]),
+    'b2g_gae_episode_major': (c_int, [P, P, c_float, c_float, P, P, c_int64, c_int, P]),
+    'b2g_discount_cumsum_f64': (c_int, [P, c_double, P, c_int64, c_int, P]),
+    'b2g_moments_ws_bytes': (c_int64, []),
+    'b2g_moments': (c_int, [P, c_int64, P, P, P]),
+    'b2g_normalize_adv': (c_int, [P, P, c_int, c_int, P, c_int64, P]),
+}
+
+
+class B2GError(RuntimeError):
+    pass
+
+
+_lib = None
+
+
+def load():
+    """Load libb2g.so once; raise if it was not built (no CPU path exists)."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise B2GError(
+            'libb2g.so not found at {}: build it with `python -m garage_b200.csrc.build` '
+            '(garage_b200 has no CPU fallback)'.format(LIB_PATH))
+    lib = ctypes.CDLL(LIB_PATH)
+    for name, (res, args) in SIGNATURES.items():
+        fn = getattr(lib, name)  # AttributeError if the symbol is not exported
+        fn.restype = res
+        fn.argtypes = args
+    _lib = lib
+    return lib
+
+
+def check(code, what=''):
+    if code != 0:
+        msg = load().b2g_last_error()
+        raise B2GError('{} failed with code {}: {}'.format(
+            what or 'libb2g call', code, msg.decode() if msg else ''))
+
+
+def ptr(t):
+    """Device pointer of a tensor (None -> NULL)."""
+    if t is None:
+        return None
+    return t.data_ptr()
+
+
+def stream_ptr(device=None):
+    return torch.cuda.current_stream(device).cuda_stream
+
+
+def require_cuda(*tensors):
+    for t in tensors:
+        if t is not None and not t.is_cuda:
+            raise B2GError('libb2g needs CUDA tensors (there is no CPU path); got device {}'.format(t.device))
+
+
+def call(name, *args):
+    lib = load()
+    code = getattr(lib, name)(*args)
+    check(code, name)

@@ -1,0 +1,238 @@
+// GAE advantages + discounted returns: reverse (segmented) linear-recurrence scans.
+//   replaces garage torch/_functions.py:25-85 (compute_advantages, pad + conv2d,
+//   O(N*P^2)) and np/_functions.py:111-128 (discount_cumsum, scipy lfilter per row).
+// HBM-bound: 17 algorithmic bytes per (t,n) element when fused
+//   (r 4 + V 4 + step_type 1 read, A 4 + R 4 written).
+#include "common.cuh"
+
+// ------------------------------------------------------ time-major kernel --
+// One thread per environment column n, sequential over t (the recurrence), the
+// warp covers 32 consecutive n => every access is one full 128 B line.  The
+// loads do not depend on the carry, so U rows are prefetched into registers
+// (double buffered) to keep U*9 B per thread in flight; U is picked by the host
+// from N so that bytes-in-flight cover HBM latency even when N is small.
+template <int U, bool HAS_ST, bool HAS_ADV, bool HAS_RET>
+__global__ void __launch_bounds__(256)
+gae_time_major_kernel(const float* __restrict__ rew, const float* __restrict__ val,
+                      const uint8_t* __restrict__ st, const float* __restrict__ last_val,
+                      float gamma, float gl, float* __restrict__ adv,
+                      float* __restrict__ ret, int T, int64_t N) {
+    const int64_t n = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (n >= N) return;
+    float next_v = last_val ? last_val[n] : 0.0f;
+    float ca = 0.0f, cr = 0.0f;
+
+    float r0[U], v0[U], r1[U], v1[U];
+    uint8_t s0[U], s1[U];
+
+    auto load = [&](int t_hi, float* r, float* v, uint8_t* s) {
+#pragma unroll
+        for (int j = 0; j < U; ++j) {
+            const int t = t_hi - 1 - j;
+            if (t >= 0) {
+                const int64_t i = (int64_t)t * N + n;
+                r[j] = __ldcs(rew + i);
+                if (HAS_ADV) v[j] = __ldcs(val + i);
+                if (HAS_ST) s[j] = __ldcs(st + i);
+            }
+        }
+    };
+    auto consume = [&](int t_hi, const float* r, const float* v, const uint8_t* s) {
+#pragma unroll
+        for (int j = 0; j < U; ++j) {
+            const int t = t_hi - 1 - j;
+            if (t >= 0) {
+                const int64_t i = (int64_t)t * N + n;
+                if (HAS_ST && s[j] >= ST_TERMINAL) {  // episode ends here: cut carries
+                    ca = 0.0f; cr = 0.0f; next_v = 0.0f;
+                }
+                if (HAS_ADV) {
+                    const float delta = r[j] + gamma * next_v - v[j];
+                    ca = delta + gl * ca;
+                    next_v = v[j];
+                    __stcs(adv + i, ca);
+                }
+                if (HAS_RET) {
+                    cr = r[j] + gamma * cr;
+                    __stcs(ret + i, cr);
+                }
+            }
+        }
+    };
+
+    int t_hi = T;
+    load(t_hi, r0, v0, s0);
+    while (t_hi > 0) {
+        load(t_hi - U, r1, v1, s1);
+        consume(t_hi, r0, v0, s0);
+        t_hi -= U;
+        if (t_hi <= 0) break;
+        load(t_hi - U, r0, v0, s0);
+        consume(t_hi, r1, v1, s1);
+        t_hi -= U;
+    }
+}
+
+template <int U>
+static int launch_time_major(const float* rew, const float* val, const uint8_t* st,
+                             const float* last_val, float gamma, float lam, float* adv,
+                             float* ret, int T, int64_t N, cudaStream_t s) {
+    const int threads = (N >= 148 * 256) ? 256 : (N >= 148 * 64 ? 64 : 32);
+    const unsigned blocks = (unsigned)((N + threads - 1) / threads);
+    const float gl = gamma * lam;
+#define B2G_GAE_LAUNCH(ST, A, R)                                                          \
+    gae_time_major_kernel<U, ST, A, R><<<blocks, threads, 0, s>>>(rew, val, st, last_val, \
+                                                                   gamma, gl, adv, ret, T, N)
+    const bool hs = st != nullptr, ha = adv != nullptr, hr = ret != nullptr;
+    if (hs && ha && hr) B2G_GAE_LAUNCH(true, true, true);
+    else if (hs && ha && !hr) B2G_GAE_LAUNCH(true, true, false);
+    else if (hs && !ha && hr) B2G_GAE_LAUNCH(true, false, true);
+    else if (!hs && ha && hr) B2G_GAE_LAUNCH(false, true, true);
+    else if (!hs && ha && !hr) B2G_GAE_LAUNCH(false, true, false);
+    else B2G_GAE_LAUNCH(false, false, true);
+#undef B2G_GAE_LAUNCH
+    B2G_CHECK_LAUNCH();
+    return B2G_OK;
+}
+
+extern "C" int b2g_gae_time_major(const float* rew, const float* val,
+                                  const uint8_t* step_type, const float* last_val,
+                                  float gamma, float lam, float* adv_out, float* ret_out,
+                                  int T, int64_t N, void* stream) {
+    B2G_CHECK_ARG(T >= 0 && N >= 0, "negative shape");
+    B2G_CHECK_ARG(adv_out || ret_out, "adv_out and ret_out are both NULL");
+    B2G_CHECK_ARG(rew != nullptr || T * N == 0, "rew is NULL");
+    B2G_CHECK_ARG(!adv_out || val != nullptr || T * N == 0, "val is NULL but adv_out given");
+    if (T == 0 || N == 0) return B2G_OK;
+    cudaStream_t s = (cudaStream_t)stream;
+    // bytes in flight ~ N * U * 9: aim for >= ~6 MB (HBM latency x bandwidth)
+    if (N >= (1 << 17)) return launch_time_major<4>(rew, val, step_type, last_val, gamma, lam, adv_out, ret_out, T, N, s);
+    if (N >= (1 << 16)) return launch_time_major<8>(rew, val, step_type, last_val, gamma, lam, adv_out, ret_out, T, N, s);
+    if (N >= (1 << 15)) return launch_time_major<16>(rew, val, step_type, last_val, gamma, lam, adv_out, ret_out, T, N, s);
+    return launch_time_major<32>(rew, val, step_type, last_val, gamma, lam, adv_out, ret_out, T, N, s);
+}
+
+// --------------------------------------------------- episode-major kernel --
+// garage's own layout: rows = episodes [N,P], zero padded.  One warp per row,
+// lanes cover 32 consecutive time steps (one 128 B line), segments walked from
+// the end of the row.  Inside a segment the recurrence x_t += c * x_{t+1} is a
+// Kogge-Stone scan over affine maps with warp shuffles (5 steps, powers
+// c, c^2, c^4, c^8, c^16); across segments a scalar carry is applied with
+// c^(32-lane).
+template <typename F>
+__device__ __forceinline__ F warp_reverse_decay_scan(F x, const F* cpow, int lane) {
+#pragma unroll
+    for (int k = 0; k < 5; ++k) {
+        const int d = 1 << k;
+        const F y = __shfl_down_sync(0xffffffffu, x, d);
+        if (lane + d < 32) x += cpow[k] * y;
+    }
+    return x;
+}
+
+template <bool HAS_RET>
+__global__ void __launch_bounds__(256)
+gae_episode_major_kernel(const float* __restrict__ base, const float* __restrict__ rew,
+                         float gamma, float gl, float* __restrict__ adv,
+                         float* __restrict__ ret, int64_t N, int P) {
+    const int lane = threadIdx.x & 31;
+    const int64_t row = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    if (row >= N) return;
+    float pa[5], pr[5];
+    pa[0] = gl; pr[0] = gamma;
+#pragma unroll
+    for (int k = 1; k < 5; ++k) { pa[k] = pa[k - 1] * pa[k - 1]; pr[k] = pr[k - 1] * pr[k - 1]; }
+    // c^(32-lane): lane 31 -> c, lane 0 -> c^32
+    float ta = 1.0f, tr = 1.0f;
+    {
+        const int e = 32 - lane;
+#pragma unroll
+        for (int k = 0; k < 5; ++k)
+            if (e & (1 << k)) { ta *= pa[k]; tr *= pr[k]; }
+        if (e & 32) { ta = pa[4] * pa[4]; tr = pr[4] * pr[4]; }
+    }
+    const float* b = base + row * (int64_t)P;
+    const float* r = rew + row * (int64_t)P;
+    float carry_a = 0.0f, carry_r = 0.0f, v_next_seg = 0.0f;  // V_P := 0
+    const int nseg = (P + 31) >> 5;
+    for (int sgm = nseg - 1; sgm >= 0; --sgm) {
+        const int t = (sgm << 5) + lane;
+        const bool in = t < P;
+        const float vt = in ? __ldcs(b + t) : 0.0f;
+        const float rt = in ? __ldcs(r + t) : 0.0f;
+        float vn = __shfl_down_sync(0xffffffffu, vt, 1);
+        if (lane == 31) vn = v_next_seg;
+        if (t + 1 >= P) vn = 0.0f;
+        float xa = in ? (rt + gamma * vn - vt) : 0.0f;
+        xa = warp_reverse_decay_scan(xa, pa, lane) + ta * carry_a;
+        if (in) __stcs(adv + row * (int64_t)P + t, xa);
+        carry_a = __shfl_sync(0xffffffffu, xa, 0);
+        v_next_seg = __shfl_sync(0xffffffffu, vt, 0);
+        if (HAS_RET) {
+            float xr = warp_reverse_decay_scan(rt, pr, lane) + tr * carry_r;
+            if (in) __stcs(ret + row * (int64_t)P + t, xr);
+            carry_r = __shfl_sync(0xffffffffu, xr, 0);
+        }
+    }
+}
+
+extern "C" int b2g_gae_episode_major(const float* baselines, const float* rewards,
+                                     float gamma, float lam, float* adv_out,
+                                     float* ret_out, int64_t N, int P, void* stream) {
+    B2G_CHECK_ARG(N >= 0 && P >= 0, "negative shape");
+    if (N == 0 || P == 0) return B2G_OK;
+    B2G_CHECK_ARG(baselines && rewards && adv_out, "NULL pointer");
+    const int threads = 256;
+    const unsigned blocks = (unsigned)((N * 32 + threads - 1) / threads);
+    cudaStream_t s = (cudaStream_t)stream;
+    if (ret_out)
+        gae_episode_major_kernel<true><<<blocks, threads, 0, s>>>(baselines, rewards, gamma, gamma * lam, adv_out, ret_out, N, P);
+    else
+        gae_episode_major_kernel<false><<<blocks, threads, 0, s>>>(baselines, rewards, gamma, gamma * lam, adv_out, ret_out, N, P);
+    B2G_CHECK_LAUNCH();
+    return B2G_OK;
+}
+
+// discount_cumsum on float64 rows (np/_functions.py:111-128; garage's rewards
+// are float64 python floats, vpg.py:149-153 casts the result to float32).
+__global__ void __launch_bounds__(256)
+discount_cumsum_f64_kernel(const double* __restrict__ x, double gamma,
+                           double* __restrict__ out, int64_t N, int P) {
+    const int lane = threadIdx.x & 31;
+    const int64_t row = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    if (row >= N) return;
+    double pr[5];
+    pr[0] = gamma;
+#pragma unroll
+    for (int k = 1; k < 5; ++k) pr[k] = pr[k - 1] * pr[k - 1];
+    double tr = 1.0;
+    {
+        const int e = 32 - lane;
+#pragma unroll
+        for (int k = 0; k < 5; ++k)
+            if (e & (1 << k)) tr *= pr[k];
+        if (e & 32) tr = pr[4] * pr[4];
+    }
+    double carry = 0.0;
+    const int nseg = (P + 31) >> 5;
+    for (int sgm = nseg - 1; sgm >= 0; --sgm) {
+        const int t = (sgm << 5) + lane;
+        const bool in = t < P;
+        double xr = in ? x[row * (int64_t)P + t] : 0.0;
+        xr = warp_reverse_decay_scan(xr, pr, lane) + tr * carry;
+        if (in) out[row * (int64_t)P + t] = xr;
+        carry = __shfl_sync(0xffffffffu, xr, 0);
+    }
+}
+
+extern "C" int b2g_discount_cumsum_f64(const double* x, double gamma, double* out,
+                                       int64_t N, int P, void* stream) {
+    B2G_CHECK_ARG(N >= 0 && P >= 0, "negative shape");
+    if (N == 0 || P == 0) return B2G_OK;
+    B2G_CHECK_ARG(x && out, "NULL pointer");
+    const int threads = 256;
+    const unsigned blocks = (unsigned)((N * 32 + threads - 1) / threads);
+    discount_cumsum_f64_kernel<<<blocks, threads, 0, (cudaStream_t)stream>>>(x, gamma, out, N, P);
+    B2G_CHECK_LAUNCH();
+    return B2G_OK;
+}
