@@ -20,7 +20,9 @@ gae_time_major_kernel(const float* __restrict__ rew, const float* __restrict__ v
     const int64_t n = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (n >= N) return;
     float next_v = last_val ? last_val[n] : 0.0f;
-    float ca = 0.0f, cr = 0.0f;
+    float ca = 0.0f;
+    double cr = 0.0;  // returns accumulate in fp64 like the reference (float64 lfilter, then cast)
+    const double gamma_d = (double)gamma;
 
     float r0[U], v0[U], r1[U], v1[U];
     uint8_t s0[U], s1[U];
@@ -44,7 +46,7 @@ gae_time_major_kernel(const float* __restrict__ rew, const float* __restrict__ v
             if (t >= 0) {
                 const int64_t i = (int64_t)t * N + n;
                 if (HAS_ST && s[j] >= ST_TERMINAL) {  // episode ends here: cut carries
-                    ca = 0.0f; cr = 0.0f; next_v = 0.0f;
+                    ca = 0.0f; cr = 0.0; next_v = 0.0f;
                 }
                 if (HAS_ADV) {
                     const float delta = r[j] + gamma * next_v - v[j];
@@ -53,8 +55,8 @@ gae_time_major_kernel(const float* __restrict__ rew, const float* __restrict__ v
                     __stcs(adv + i, ca);
                 }
                 if (HAS_RET) {
-                    cr = r[j] + gamma * cr;
-                    __stcs(ret + i, cr);
+                    cr = (double)r[j] + gamma_d * cr;
+                    __stcs(ret + i, (float)cr);
                 }
             }
         }
@@ -153,7 +155,20 @@ gae_episode_major_kernel(const float* __restrict__ base, const float* __restrict
     }
     const float* b = base + row * (int64_t)P;
     const float* r = rew + row * (int64_t)P;
-    float carry_a = 0.0f, carry_r = 0.0f, v_next_seg = 0.0f;  // V_P := 0
+    double prd[5];
+    prd[0] = (double)gamma;
+#pragma unroll
+    for (int k = 1; k < 5; ++k) prd[k] = prd[k - 1] * prd[k - 1];
+    double trd = 1.0;
+    {
+        const int e = 32 - lane;
+#pragma unroll
+        for (int k = 0; k < 5; ++k)
+            if (e & (1 << k)) trd *= prd[k];
+        if (e & 32) trd = prd[4] * prd[4];
+    }
+    float carry_a = 0.0f, v_next_seg = 0.0f;  // V_P := 0
+    double carry_r = 0.0;
     const int nseg = (P + 31) >> 5;
     for (int sgm = nseg - 1; sgm >= 0; --sgm) {
         const int t = (sgm << 5) + lane;
@@ -169,8 +184,9 @@ gae_episode_major_kernel(const float* __restrict__ base, const float* __restrict
         carry_a = __shfl_sync(0xffffffffu, xa, 0);
         v_next_seg = __shfl_sync(0xffffffffu, vt, 0);
         if (HAS_RET) {
-            float xr = warp_reverse_decay_scan(rt, pr, lane) + tr * carry_r;
-            if (in) __stcs(ret + row * (int64_t)P + t, xr);
+            // fp64 like the reference: discount_cumsum on float64 rewards, cast after
+            double xr = warp_reverse_decay_scan((double)rt, prd, lane) + trd * carry_r;
+            if (in) __stcs(ret + row * (int64_t)P + t, (float)xr);
             carry_r = __shfl_sync(0xffffffffu, xr, 0);
         }
     }

@@ -67,9 +67,9 @@ int b2g_gae_time_major(const float* rew, const float* val, const uint8_t* step_t
 /* b2g_gae_episode_major: same recurrences over garage's own layout,
  * baselines/rewards [N,P] row-major, zero padded (the exact signature of
  * torch/_functions.py:25 compute_advantages; V_P := 0).  One warp per episode,
- * warp-shuffle affine scan over 32-step segments.  ret_out may be NULL;
- * rewards64 (double, may be NULL) when given is the source of the returns,
- * matching vpg.py:149-153 which runs discount_cumsum on float64 rewards.
+ * warp-shuffle affine scan over 32-step segments.  ret_out may be NULL; the
+ * returns scan runs in float64 and is cast at the end, as vpg.py:149-153 does
+ * (discount_cumsum on float64, then torch.Tensor()).
  */
 int b2g_gae_episode_major(const float* baselines, const float* rewards, float gamma,
                           float lam, float* adv_out, float* ret_out, int64_t N, int P,
@@ -93,6 +93,122 @@ int b2g_moments(const float* x, int64_t n, double* out3, void* ws, void* stream)
  * minimum of the centred values (== (min - mean)/(var+eps)). */
 int b2g_normalize_adv(const float* x, const double* stats3, int center_adv,
                       int positive_adv, float* y, int64_t n, void* stream);
+
+/* ------------------------------------------------------------------ envs --
+ * GPU-resident batched environments.  env_id selects the dynamics; `params`
+ * is a HOST array of B2G_ENV_NPARAMS doubles:
+ *   B2G_ENV_POINT    (envs/point_env.py:25-162; obs 3, act 2, state 2)
+ *       [goal_x, goal_y, arena_size, done_bonus, never_done]
+ *   B2G_ENV_PENDULUM (gym==0.17.2 pendulum.py behind envs/gym_env.py:182-270;
+ *                     obs 3, act 1, state 2 = theta, theta_dot)
+ *       [max_speed 8, max_torque 2, dt .05, g 10, m 1, l 1]
+ *   B2G_ENV_CARTPOLE (gym==0.17.2 cartpole.py, "CartPole-style" continuous
+ *                     action; obs 4, act 1, state 4)
+ *       [gravity 9.8, masscart 1, masspole .1, length .5, force_mag 10, tau .02,
+ *        x_threshold 2.4, theta_threshold 12 deg in rad,
+ *        act_mode (0: force = +F if a > 0 else -F; 1: force = F*clip(a,-1,1))]
+ * state is float64 SoA [S, N] (gym integrates in float64; PointEnv's float32
+ * values are stored exactly), step_cnt int32 [N] (-1 = reset() needed, the
+ * reference's `_step_cnt = None`), episode int32 [N] counts resets per env and
+ * indexes the Philox reset stream so that results do not depend on sharding:
+ * global env id = env_id_offset + n.
+ */
+#define B2G_ENV_POINT 0
+#define B2G_ENV_PENDULUM 1
+#define B2G_ENV_CARTPOLE 2
+#define B2G_ENV_NPARAMS 10
+
+int b2g_env_obs_dim(int env_id);
+int b2g_env_act_dim(int env_id);
+int b2g_env_state_dim(int env_id);
+
+/* Environment.reset() for all N envs: point_env.py:79-98 / gym_env.py:182-199.
+ * Writes state, obs[N,O] (float32), step_cnt := 0, episode[n] += 1. */
+int b2g_env_reset(int env_id, const double* params, uint64_t seed, int64_t env_id_offset,
+                  double* state, float* obs, int32_t* step_cnt, int32_t* episode, int64_t N,
+                  void* stream);
+
+/* Environment.step(action) for all N envs, ONE step, no auto-reset (the
+ * replay-parity entry point): point_env.py:100-162 / gym_env.py:201-270.
+ * actions[N,A] float32 (stored un-clipped by the caller, point_env.py:155);
+ * obs_out[N,O] float32; reward_out[N] float64 (python float in the reference);
+ * step_type_out[N] uint8 via StepType.get_step_type (_dtypes.py:44-68);
+ * success_out[N] uint8 or NULL (PointEnv env_info['success']).
+ * An env whose step_cnt is -1 ("reset() must be called before step()",
+ * point_env.py:113-114) is left untouched and *err_flag (device int32, may be
+ * NULL) is set to 1 + its index; the host wrapper raises RuntimeError.  On a
+ * TERMINAL/TIMEOUT step step_cnt becomes -1 (point_env.py:147-148). */
+int b2g_env_step(int env_id, const double* params, int max_episode_length, double* state,
+                 const float* actions, float* obs_out, double* reward_out,
+                 uint8_t* step_type_out, uint8_t* success_out, int32_t* step_cnt,
+                 int32_t* err_flag, int64_t N, void* stream);
+
+/* --------------------------------------------------------------- rollout --
+ * Policy parameter vector (float32, the order of GaussianMLPPolicy.state_dict(),
+ * torch/policies/gaussian_mlp_policy.py:53-87 with hidden_sizes=(H,H)):
+ *   [ log_std (1) | W1 [H,O] | b1 [H] | W2 [H,H] | b2 [H] | W3 [A,H] | b3 [A] ]
+ * b2g_mlp_param_count gives its length.  H in {32, 64}; other sizes return
+ * B2G_ERR_UNSUPPORTED (never a silent fallback).
+ */
+int64_t b2g_mlp_param_count(int obs_dim, int hidden, int out_dim);
+
+/* b2g_rollout: n_steps of  get_actions -> env.step -> bookkeeping  for N envs in
+ * ONE persistent launch; replaces the Python loop of sampler/vec_worker.py:176-204
+ * (+ _gather_episode :139-174, default_worker.py:100-122) and the policy
+ * forward/sample of torch/policies/stochastic_policy.py:46-89.
+ *   in/out (persist across calls): state[S,N] f64, cur_obs[N,O], step_cnt[N],
+ *     episode[N] (as b2g_env_reset leaves them).
+ *   min/max_log_std: log(min_std) / log(max_std) clamps of
+ *     gaussian_mlp_module.py:171-176 (+-INFINITY for None).
+ *   Philox counter = (env_id_offset + n, t_counter + t): results do not depend
+ *     on how envs are sharded over ranks or on chunking over time.
+ *   out, time-major rows t = 0..n_steps-1: obs[T,N,O] (observation the action
+ *     was computed from), act[T,N,A] (un-clipped sample), rew[T,N] f32,
+ *     logp[T,N] (log-prob of act under the rollout policy == PPO's old_ll, Q8),
+ *     step_type[T,N] u8, mean[T,N,A] (agent_info, may be NULL),
+ *     success[T,N] u8 (PointEnv env_info, may be NULL), last_obs[T,N,O]
+ *     (may be NULL; written only on TERMINAL/TIMEOUT rows: the post-step
+ *     observation that EpisodeBatch.last_observations holds, Q10),
+ *     ep_len[T,N] i32 (may be NULL; written on TERMINAL/TIMEOUT rows only:
+ *     the length of the episode that ends there, input of b2g_pack_*).
+ *   An env that finishes is reset in the same step (vec_worker.py:171).
+ */
+int b2g_rollout(int env_id, const double* params, int max_episode_length,
+                const float* policy_params, int hidden, float min_log_std, float max_log_std,
+                uint64_t seed, int64_t env_id_offset, uint32_t t_counter, double* state,
+                float* cur_obs, int32_t* step_cnt, int32_t* episode, int n_steps, int64_t N,
+                float* obs, float* act, float* rew, float* logp, uint8_t* step_type,
+                float* mean, uint8_t* success, float* last_obs, int32_t* ep_len, void* stream);
+
+/* ------------------------------------------------------- EpisodeBatch pack --
+ * Time-major rollout buffers -> garage's episode-major packed EpisodeBatch
+ * layout; replaces sampler/vec_worker.py:139-174,206-219, the ">= num_samples,
+ * whole episodes" loop of sampler/local_sampler.py:156-166 and
+ * EpisodeBatch.concatenate (_dtypes.py:591-632).  Episodes are ordered by
+ * completion row, ties by env index.
+ *  b2g_pack_plan:  per-row episode/step counts, exclusive scans, the cut row.
+ *     summary4 (device int64[4]) = [t_star, n_eps, n_steps, reached]; reached=0
+ *     means the buffer holds fewer than num_samples completed steps (run more
+ *     rows and call again).  ws: b2g_pack_ws_bytes(T).
+ *  b2g_pack_index: lengths_out[n_eps] (int64, numpy 'l' like vec_worker.py:162),
+ *     ep_off[T,N] (int64, sparse: packed offset of the episode that ends at
+ *     (t,n)), last_observations_out[n_eps,O], ep_env_out/ep_end_out[n_eps]
+ *     (env index / last row of each episode; may be NULL).  T_used = t_star+1,
+ *     T_ws = the T given to b2g_pack_plan.
+ *  b2g_pack_fields: scatter up to 12 per-step fields (src [T,N,w] -> dst
+ *     [n_steps,w]); bytes_per_step[k] is 1 (uint8) or a multiple of 4.  src/dst/
+ *     bytes_per_step are HOST arrays of n_fields entries.
+ */
+int64_t b2g_pack_ws_bytes(int T);
+int b2g_pack_plan(const uint8_t* step_type, const int32_t* ep_len, int T, int64_t N,
+                  int64_t num_samples, void* ws, int64_t* summary4, void* stream);
+int b2g_pack_index(const uint8_t* step_type, const int32_t* ep_len, const float* last_obs,
+                   int obs_dim, int T_used, int T_ws, int64_t N, const void* ws,
+                   int64_t* lengths_out, int64_t* ep_off, float* last_observations_out,
+                   int32_t* ep_env_out, int32_t* ep_end_out, void* stream);
+int b2g_pack_fields(const uint8_t* step_type, const int32_t* ep_len, const int64_t* ep_off,
+                    int T_used, int64_t N, int n_fields, const void* const* src,
+                    void* const* dst, const int* bytes_per_step, void* stream);
 
 #ifdef __cplusplus
 }

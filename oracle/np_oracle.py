@@ -88,7 +88,7 @@ def gae_time_major(rew, val, step_type, last_val, discount, gae_lambda):
     gl = np.float32(np.float32(discount) * np.float32(gae_lambda))
     nv = np.zeros(N, np.float32) if last_val is None else np.asarray(last_val, np.float32).copy()
     ca = np.zeros(N, np.float32)
-    cr = np.zeros(N, np.float32)
+    cr = np.zeros(N, np.float64)  # returns: float64 lfilter then cast (vpg.py:149-153)
     for t in range(T - 1, -1, -1):
         if step_type is not None:
             cut = np.asarray(step_type[t]) >= TERMINAL
@@ -97,7 +97,7 @@ def gae_time_major(rew, val, step_type, last_val, discount, gae_lambda):
             nv[cut] = 0
         delta = (rew[t] + g * nv - val[t]).astype(np.float32)
         ca = (delta + gl * ca).astype(np.float32)
-        cr = (rew[t] + g * cr).astype(np.float32)
+        cr = rew[t].astype(np.float64) + float(discount) * cr
         nv = val[t].copy()
         adv[t] = ca
         ret[t] = cr
