@@ -1,0 +1,197 @@
+// Host launchers for the fused MLP minibatch kernel, partial-gradient reduction,
+// Adam, and the forward-only evaluation paths.
+#include "mlp_train.cuh"
+
+// CTAs per launch: one per 128-row tile, capped at SMs x resident CTAs per SM
+// (persistent grid-stride over tiles beyond that).
+template <int H, int O, int A, bool BWD>
+static int mlp_occupancy() {
+    static int occ = 0;
+    if (occ == 0) {
+        constexpr size_t smem = mlp_train_smem_bytes<H, O, A, BWD>();
+        cudaFuncSetAttribute(mlp_train_kernel<H, O, A, BWD>,
+                             cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        int n = 0;
+        if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, mlp_train_kernel<H, O, A, BWD>,
+                                                          MLP_NT, smem) != cudaSuccess || n < 1)
+            n = 1;
+        occ = n;
+    }
+    return occ;
+}
+
+template <int H, int O, int A, bool BWD>
+static int mlp_grid(int64_t rows) {
+    const int64_t tiles = (rows + MLP_R - 1) / MLP_R;
+    const int64_t cap = (int64_t)b2g_sm_count() * mlp_occupancy<H, O, A, BWD>();
+    return (int)(tiles < cap ? (tiles > 0 ? tiles : 1) : cap);
+}
+
+template <int H, int O, int A, bool BWD>
+static int launch_mlp(const MlpArgs& a, cudaStream_t s) {
+    constexpr size_t smem = mlp_train_smem_bytes<H, O, A, BWD>();
+    const int grid = mlp_grid<H, O, A, BWD>(a.mb);
+    mlp_train_kernel<H, O, A, BWD><<<grid, MLP_NT, smem, s>>>(a);
+    B2G_CHECK_LAUNCH();
+    return B2G_OK;
+}
+
+#define B2G_MLP_SHAPES(X) X(64, 3, 1) X(64, 3, 2) X(64, 4, 1) X(32, 3, 1) X(32, 3, 2) X(32, 4, 1)
+
+static int mlp_unsupported(int O, int H, int A) {
+    b2g_set_error("MLP shape obs=%d hidden=(%d,%d) out=%d is not built into libb2g "
+                  "(built: obs in {3,4}, hidden in {32,64}, out in {1,2})", O, H, H, A);
+    return B2G_ERR_UNSUPPORTED;
+}
+
+template <bool BWD>
+static int dispatch_mlp(int O, int H, int A, const MlpArgs& a, cudaStream_t s) {
+#define B2G_CASE(HH, OO, AA) \
+    if (H == HH && O == OO && A == AA) return launch_mlp<HH, OO, AA, BWD>(a, s);
+    B2G_MLP_SHAPES(B2G_CASE)
+#undef B2G_CASE
+    return mlp_unsupported(O, H, A);
+}
+
+// number of per-CTA partial rows a launch over `rows` rows writes (<0: unsupported shape)
+extern "C" int b2g_mlp_num_partials(int obs_dim, int hidden, int out_dim, int backward,
+                                    int64_t rows) {
+#define B2G_CASE(HH, OO, AA)                                               \
+    if (hidden == HH && obs_dim == OO && out_dim == AA)                    \
+        return backward ? mlp_grid<HH, OO, AA, true>(rows) : mlp_grid<HH, OO, AA, false>(rows);
+    B2G_MLP_SHAPES(B2G_CASE)
+#undef B2G_CASE
+    return mlp_unsupported(obs_dim, hidden, out_dim);
+}
+
+// floats of workspace that any launch for this shape can need
+extern "C" int64_t b2g_mlp_ws_floats(int obs_dim, int hidden, int out_dim) {
+    const int P = MlpLayout{obs_dim, hidden, out_dim}.total();
+    return (int64_t)b2g_sm_count() * 4 * (P + MLP_NSTATS);
+}
+
+extern "C" int b2g_mlp_minibatch_grad(int obs_dim, int hidden, int out_dim, const float* params,
+                                      const int32_t* idx, int64_t start, int64_t mb,
+                                      const float* obs, const float* act, const float* adv,
+                                      const float* old_logp, const float* ret, int loss_kind,
+                                      int flags, float clip, float ent_coeff, float min_log_std,
+                                      float max_log_std, float* ws_partial,
+                                      unsigned long long* step_counter, void* stream) {
+    B2G_CHECK_ARG(mb > 0, "empty minibatch");
+    B2G_CHECK_ARG(params && obs && ws_partial, "NULL pointer");
+    B2G_CHECK_ARG(loss_kind >= LOSS_PPO && loss_kind <= LOSS_VF, "bad loss_kind");
+    if (loss_kind == LOSS_VF) B2G_CHECK_ARG(ret != nullptr && out_dim == 1, "value loss needs ret and out_dim 1");
+    else B2G_CHECK_ARG(act && adv && (loss_kind != LOSS_PPO || old_logp), "policy loss needs act, adv (and old_logp for PPO)");
+    MlpArgs a{};
+    a.params = params; a.idx = idx; a.start = start; a.mb = mb; a.obs = obs; a.act = act;
+    a.adv = adv; a.old_logp = old_logp; a.ret = ret; a.old_mean = nullptr; a.old_log_std = 0.f;
+    a.loss_kind = loss_kind; a.flags = flags; a.clip = clip; a.ent_coeff = ent_coeff;
+    a.min_log_std = min_log_std; a.max_log_std = max_log_std; a.partial = ws_partial;
+    a.mean_out = nullptr; a.step_counter = step_counter;
+    return dispatch_mlp<true>(obs_dim, hidden, out_dim, a, (cudaStream_t)stream);
+}
+
+extern "C" int b2g_mlp_eval(int obs_dim, int hidden, int out_dim, const float* params,
+                            const int32_t* idx, int64_t start, int64_t n, const float* obs,
+                            const float* act, const float* adv, const float* old_logp,
+                            const float* ret, const float* old_mean, float old_log_std,
+                            int loss_kind, int flags, float clip, float ent_coeff,
+                            float min_log_std, float max_log_std, float* mean_out,
+                            float* ws_partial, void* stream) {
+    B2G_CHECK_ARG(n > 0, "empty batch");
+    B2G_CHECK_ARG(params && obs && ws_partial, "NULL pointer");
+    B2G_CHECK_ARG(loss_kind >= LOSS_PPO && loss_kind <= LOSS_NONE, "bad loss_kind");
+    if (loss_kind == LOSS_VF) B2G_CHECK_ARG(ret != nullptr && out_dim == 1, "value loss needs ret and out_dim 1");
+    else if (loss_kind != LOSS_NONE) B2G_CHECK_ARG(act && adv && (loss_kind != LOSS_PPO || old_logp), "policy loss needs act, adv (and old_logp for PPO)");
+    MlpArgs a{};
+    a.params = params; a.idx = idx; a.start = start; a.mb = n; a.obs = obs; a.act = act;
+    a.adv = adv; a.old_logp = old_logp; a.ret = ret; a.old_mean = old_mean; a.old_log_std = old_log_std;
+    a.loss_kind = loss_kind; a.flags = flags; a.clip = clip; a.ent_coeff = ent_coeff;
+    a.min_log_std = min_log_std; a.max_log_std = max_log_std; a.partial = ws_partial;
+    a.mean_out = mean_out; a.step_counter = nullptr;
+    return dispatch_mlp<false>(obs_dim, hidden, out_dim, a, (cudaStream_t)stream);
+}
+
+// ------------------------------------------------ partial reduction + Adam --
+// grad[p] = scale * sum_b partial[b][p] (fixed order -> deterministic);
+// stats[s] = sum_b partial[b][P+s] in fp64.  With `params` given, applies
+// torch.optim.Adam's single-tensor update (make_optimizer, _functions.py:25-65;
+// amsgrad=False, weight_decay=0) in the same pass.
+__global__ void __launch_bounds__(256)
+reduce_adam_kernel(const float* __restrict__ partial, int nb, int P, float scale,
+                   float* __restrict__ grad_out, double* __restrict__ stats_out,
+                   float* __restrict__ params, float* __restrict__ m, float* __restrict__ v,
+                   const unsigned long long* __restrict__ step, double lr, double beta1,
+                   double beta2, double eps) {
+    const int p = blockIdx.x * blockDim.x + threadIdx.x;
+    const int W = P + MLP_NSTATS;
+    if (p >= W) return;
+    if (p >= P) {
+        double s = 0.0;
+        for (int b = 0; b < nb; ++b) s += (double)partial[(int64_t)b * W + p];
+        if (stats_out) stats_out[p - P] = s;
+        return;
+    }
+    float s = 0.0f;
+#pragma unroll 8
+    for (int b = 0; b < nb; ++b) s += partial[(int64_t)b * W + p];
+    const float g = s * scale;
+    if (grad_out) grad_out[p] = g;
+    if (params) {
+        const double t = (double)(*step);
+        const double bc1 = 1.0 - pow(beta1, t), bc2 = 1.0 - pow(beta2, t);
+        const float step_size = (float)(lr / bc1);
+        const float bc2_sqrt = (float)sqrt(bc2);
+        float mm = m[p], vv = v[p];
+        mm = mm + (float)(1.0 - beta1) * (g - mm);                  // exp_avg.lerp_(grad, 1-beta1)
+        vv = vv * (float)beta2 + ((float)(1.0 - beta2) * g) * g;     // mul_(beta2).addcmul_(g, g, 1-beta2)
+        const float denom = sqrtf(vv) / bc2_sqrt + (float)eps;
+        params[p] = params[p] - step_size * (mm / denom);           // addcdiv_(exp_avg, denom, -step_size)
+        m[p] = mm; v[p] = vv;
+    }
+}
+
+extern "C" int b2g_mlp_reduce(const float* ws_partial, int n_partials, int n_params, float scale,
+                              float* grad_out, double* stats_out, float* params, float* adam_m,
+                              float* adam_v, const unsigned long long* step_counter, double lr,
+                              double beta1, double beta2, double eps, void* stream) {
+    B2G_CHECK_ARG(ws_partial && n_partials > 0 && n_params > 0, "bad arguments");
+    B2G_CHECK_ARG(!params || (adam_m && adam_v && step_counter), "Adam needs m, v and the step counter");
+    const int W = n_params + MLP_NSTATS;
+    reduce_adam_kernel<<<(W + 255) / 256, 256, 0, (cudaStream_t)stream>>>(
+        ws_partial, n_partials, n_params, scale, grad_out, stats_out, params, adam_m, adam_v,
+        step_counter, lr, beta1, beta2, eps);
+    B2G_CHECK_LAUNCH();
+    return B2G_OK;
+}
+
+// Adam alone, on an (all-reduced) gradient vector.
+__global__ void __launch_bounds__(256)
+adam_kernel(float* __restrict__ params, const float* __restrict__ grad, float gscale,
+            float* __restrict__ m, float* __restrict__ v,
+            const unsigned long long* __restrict__ step, double lr, double beta1, double beta2,
+            double eps, int n) {
+    const int p = blockIdx.x * blockDim.x + threadIdx.x;
+    if (p >= n) return;
+    const double t = (double)(*step);
+    const double bc1 = 1.0 - pow(beta1, t), bc2 = 1.0 - pow(beta2, t);
+    const float step_size = (float)(lr / bc1);
+    const float bc2_sqrt = (float)sqrt(bc2);
+    const float g = grad[p] * gscale;
+    float mm = m[p], vv = v[p];
+    mm = mm + (float)(1.0 - beta1) * (g - mm);
+    vv = vv * (float)beta2 + ((float)(1.0 - beta2) * g) * g;
+    const float denom = sqrtf(vv) / bc2_sqrt + (float)eps;
+    params[p] = params[p] - step_size * (mm / denom);
+    m[p] = mm; v[p] = vv;
+}
+
+extern "C" int b2g_adam_step(float* params, const float* grad, float grad_scale, float* adam_m,
+                             float* adam_v, const unsigned long long* step_counter, double lr,
+                             double beta1, double beta2, double eps, int n, void* stream) {
+    B2G_CHECK_ARG(params && grad && adam_m && adam_v && step_counter && n > 0, "bad arguments");
+    adam_kernel<<<(n + 255) / 256, 256, 0, (cudaStream_t)stream>>>(params, grad, grad_scale, adam_m, adam_v,
+                                                                   step_counter, lr, beta1, beta2, eps, n);
+    B2G_CHECK_LAUNCH();
+    return B2G_OK;
+}

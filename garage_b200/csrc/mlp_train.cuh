@@ -18,7 +18,7 @@
 #pragma once
 #include "mlp.cuh"
 
-enum : int { LOSS_PPO = 0, LOSS_VPG = 1, LOSS_VF = 2 };
+enum : int { LOSS_PPO = 0, LOSS_VPG = 1, LOSS_VF = 2, LOSS_NONE = 3 };
 enum : int {
     FLAG_ENT_REG = 1,        // entropy_method == 'regularized' (vpg.py:341-343)
     FLAG_SOFTPLUS_ENT = 2,   // use_softplus_entropy (vpg.py:429-430)
@@ -192,3 +192,275 @@ __global__ void __launch_bounds__(MLP_NT, 1) mlp_train_kernel(const MlpArgs a) {
             }
         }
         __syncthreads();
+        // ---- 4. layer 3 + loss, one thread per row: mu = W3 h2 + b3
+        if (tid < R) {
+            float mu[A];
+#pragma unroll
+            for (int q = 0; q < A; ++q) mu[q] = sB3[q];
+#pragma unroll 8
+            for (int c = 0; c < H; ++c) {
+                const float h = sH2[c * RS + tid];
+#pragma unroll
+                for (int q = 0; q < A; ++q) mu[q] = fmaf(sW3[q * H + c], h, mu[q]);
+            }
+            float dmu[A];
+#pragma unroll
+            for (int q = 0; q < A; ++q) dmu[q] = 0.0f;
+            if (src >= 0) {
+                if (a.mean_out) {
+#pragma unroll
+                    for (int q = 0; q < A; ++q) a.mean_out[(m0 + tid) * A + q] = mu[q];
+                }
+                st_rows += 1.0f;
+                // entropy of Independent(Normal): sum_a 0.5 + 0.5 log(2 pi) + log(std)
+                float ent = (float)A * (1.4189385332046727f + log_scale);
+                float dent_dls = (float)A;  // d entropy / d log_std
+                if (a.flags & FLAG_SOFTPLUS_ENT) {  // F.softplus(entropy), vpg.py:429-430
+                    const float sp = (ent > 20.0f) ? ent : log1pf(expf(ent));
+                    dent_dls *= (ent > 20.0f) ? 1.0f : 1.0f / (1.0f + expf(-ent));
+                    ent = sp;
+                }
+                st_ent += ent;
+                if (a.loss_kind == LOSS_NONE) {
+                    // forward only (baselines / means)
+                } else if (a.loss_kind == LOSS_VF) {
+                    // -log N(ret; mu, std): gaussian_mlp_value_function.py:81-97
+                    const float d = a.ret[src] - mu[0];
+                    st_loss += (d * d) / (2.0f * var) + log_scale + 0.9189385332046727f;
+                    dmu[0] = -d / var;                           // d loss / d mu (x 1/mb later)
+                    if (ls_pass) gLs += 1.0f - (d * d) / var;    // d loss / d log_std
+                } else {
+                    float ll = 0.0f, dsq = 0.0f, dact[A];
+#pragma unroll
+                    for (int q = 0; q < A; ++q) {
+                        const float av = a.act[src * A + q];
+                        ll += normal_logp_term(av, mu[q], var, log_scale);
+                        dact[q] = av - mu[q];
+                        dsq += dact[q] * dact[q];
+                    }
+                    const float adv = a.adv[src];
+                    float obj, dobj_dll;
+                    if (a.loss_kind == LOSS_PPO) {  // ppo.py:113-132
+                        const float ratio = expf(ll - a.old_logp[src]);
+                        const float lo = 1.0f - a.clip, hi = 1.0f + a.clip;
+                        const float rc = fminf(fmaxf(ratio, lo), hi);
+                        const float surr = ratio * adv, surr_c = rc * adv;
+                        obj = fminf(surr, surr_c);
+                        const bool inside = (ratio >= lo) && (ratio <= hi);
+                        // torch.min ties split the gradient, clamp passes it inside [lo,hi]
+                        const bool pass = inside || (surr < surr_c);
+                        dobj_dll = pass ? ratio * adv : 0.0f;
+                        if (!inside) st_clip += 1.0f;
+                    } else {  // vpg.py:452-455
+                        obj = ll * adv;
+                        dobj_dll = adv;
+                    }
+                    float dobj_dls = 0.0f;
+                    if (a.flags & FLAG_ENT_REG) {  // vpg.py:341-343
+                        obj += a.ent_coeff * ent;
+                        if (!(a.flags & FLAG_STOP_ENT_GRAD)) dobj_dls = a.ent_coeff * dent_dls;
+                    }
+                    st_loss -= obj;
+#pragma unroll
+                    for (int q = 0; q < A; ++q) dmu[q] = -dobj_dll * dact[q] / var;
+                    if (ls_pass) gLs -= dobj_dll * (dsq / var - (float)A) + dobj_dls;
+                    if (a.old_mean) {  // torch kl_normal_normal(old, new), vpg.py:381-406
+                        const float so = expf(a.old_log_std);
+                        const float vr = (so / stdv) * (so / stdv);
+#pragma unroll
+                        for (int q = 0; q < A; ++q) {
+                            const float t1 = (a.old_mean[src * A + q] - mu[q]) / stdv;
+                            st_kl += 0.5f * (vr + t1 * t1 - 1.0f - logf(vr));
+                        }
+                    }
+                }
+            }
+            if (BWD) {
+#pragma unroll
+                for (int q = 0; q < A; ++q) {
+                    sDmu[q * RS + tid] = dmu[q];
+                    gB3[q] += dmu[q];
+                }
+            }
+        }
+        if (!BWD) {
+            __syncthreads();
+            continue;
+        }
+        __syncthreads();
+        // ---- 5. dz2 = (W3^T dmu) * (1 - h2^2), in place over sH2; dW3, db2 partials
+        {
+            float dm[A][RPT];
+#pragma unroll
+            for (int q = 0; q < A; ++q)
+#pragma unroll
+                for (int p = 0; p < RPT / 4; ++p) {
+                    const float4 v = lds4(sDmu + q * RS + r0 + 4 * p);
+                    dm[q][4 * p] = v.x; dm[q][4 * p + 1] = v.y; dm[q][4 * p + 2] = v.z; dm[q][4 * p + 3] = v.w;
+                }
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+                const int c = tx + TXN * i;
+                float w3c[A];
+#pragma unroll
+                for (int q = 0; q < A; ++q) w3c[q] = sW3[q * H + c];
+#pragma unroll
+                for (int p = 0; p < RPT / 4; ++p) {
+                    const float4 hv = lds4(sH2 + c * RS + r0 + 4 * p);
+                    const float h[4] = {hv.x, hv.y, hv.z, hv.w};
+                    float dz[4];
+#pragma unroll
+                    for (int e = 0; e < 4; ++e) {
+                        float dh = 0.0f;
+#pragma unroll
+                        for (int q = 0; q < A; ++q) {
+                            dh = fmaf(w3c[q], dm[q][4 * p + e], dh);
+                            gW3[q][i] = fmaf(dm[q][4 * p + e], h[e], gW3[q][i]);
+                        }
+                        dz[e] = dh * (1.0f - h[e] * h[e]);
+                        gB2[i] += dz[e];
+                    }
+                    sts4(sH2 + c * RS + r0 + 4 * p, make_float4(dz[0], dz[1], dz[2], dz[3]));
+                }
+            }
+        }
+        __syncthreads();
+        // ---- 6a. GEMM3: dW2[c][k] += sum_r dz2[r][c] h1[r][k]   (c = tx+TXN*i, k = ty+TYN*j)
+#pragma unroll 2
+        for (int r = 0; r < R; r += 4) {
+            float4 d[4], hh[KPT];
+#pragma unroll
+            for (int i = 0; i < 4; ++i) d[i] = lds4(sH2 + (tx + TXN * i) * RS + r);
+#pragma unroll
+            for (int j = 0; j < KPT; ++j) hh[j] = lds4(sH1 + (ty + TYN * j) * RS + r);
+#pragma unroll
+            for (int i = 0; i < 4; ++i)
+#pragma unroll
+                for (int j = 0; j < KPT; ++j) {
+                    gW2[i][j] = fmaf(d[i].x, hh[j].x, gW2[i][j]);
+                    gW2[i][j] = fmaf(d[i].y, hh[j].y, gW2[i][j]);
+                    gW2[i][j] = fmaf(d[i].z, hh[j].z, gW2[i][j]);
+                    gW2[i][j] = fmaf(d[i].w, hh[j].w, gW2[i][j]);
+                }
+        }
+        // ---- 6b. GEMM2: dh1[r][k] = sum_c dz2[r][c] W2[c][k]; dz1 = dh1 (1 - h1^2); dW1, db1
+        {
+            float acc[RPT][4];
+#pragma unroll
+            for (int r = 0; r < RPT; ++r)
+#pragma unroll
+                for (int i = 0; i < 4; ++i) acc[r][i] = 0.0f;
+#pragma unroll 8
+            for (int c = 0; c < H; ++c) {
+                float av[RPT];
+#pragma unroll
+                for (int p = 0; p < RPT / 4; ++p) {
+                    const float4 v = lds4(sH2 + c * RS + r0 + 4 * p);
+                    av[4 * p] = v.x; av[4 * p + 1] = v.y; av[4 * p + 2] = v.z; av[4 * p + 3] = v.w;
+                }
+                const float4 b = lds4(sW2P + c * H + tx * 4);
+#pragma unroll
+                for (int r = 0; r < RPT; ++r) {
+                    acc[r][0] = fmaf(av[r], b.x, acc[r][0]);
+                    acc[r][1] = fmaf(av[r], b.y, acc[r][1]);
+                    acc[r][2] = fmaf(av[r], b.z, acc[r][2]);
+                    acc[r][3] = fmaf(av[r], b.w, acc[r][3]);
+                }
+            }
+            float xr[O][RPT];
+#pragma unroll
+            for (int o = 0; o < O; ++o)
+#pragma unroll
+                for (int p = 0; p < RPT / 4; ++p) {
+                    const float4 v = lds4(sX + o * RS + r0 + 4 * p);
+                    xr[o][4 * p] = v.x; xr[o][4 * p + 1] = v.y; xr[o][4 * p + 2] = v.z; xr[o][4 * p + 3] = v.w;
+                }
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+                const int k = tx + TXN * i;
+#pragma unroll
+                for (int p = 0; p < RPT / 4; ++p) {
+                    const float4 hv = lds4(sH1 + k * RS + r0 + 4 * p);
+                    const float h[4] = {hv.x, hv.y, hv.z, hv.w};
+#pragma unroll
+                    for (int e = 0; e < 4; ++e) {
+                        const float dz1 = acc[4 * p + e][i] * (1.0f - h[e] * h[e]);
+                        gB1[i] += dz1;
+#pragma unroll
+                        for (int o = 0; o < O; ++o) gW1[i][o] = fmaf(dz1, xr[o][4 * p + e], gW1[i][o]);
+                    }
+                }
+            }
+        }
+        __syncthreads();
+    }  // tiles
+
+    // ---- write this CTA's partial: [P gradients | MLP_NSTATS statistics]
+    float* out = a.partial + (int64_t)blockIdx.x * (P + MLP_NSTATS);
+    float* red = sH1;  // scratch (sH1 and sH2 are contiguous, 2*H*RS floats)
+    if (BWD) {
+#pragma unroll
+        for (int i = 0; i < 4; ++i)
+#pragma unroll
+            for (int j = 0; j < KPT; ++j)
+                out[L.off_w2() + (tx + TXN * i) * H + (ty + TYN * j)] = gW2[i][j];
+        // column-owned sums are replicated over the TYN row groups: reduce in fixed order
+        constexpr int VV = A + O + 2, V = 4 * VV;
+        static_assert(MLP_NT * V <= 2 * H * MLP_RS, "reduction scratch too small");
+        float* mine = red + (ty * TXN + tx) * V;
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+#pragma unroll
+            for (int q = 0; q < A; ++q) mine[i * VV + q] = gW3[q][i];
+            mine[i * VV + A] = gB2[i];
+#pragma unroll
+            for (int o = 0; o < O; ++o) mine[i * VV + A + 1 + o] = gW1[i][o];
+            mine[i * VV + A + O + 1] = gB1[i];
+        }
+        __syncthreads();
+        for (int e = tid; e < TXN * V; e += MLP_NT) {
+            const int txp = e / V, v = e % V, i = v / VV, s = v % VV;
+            float sum = 0.0f;
+            for (int y = 0; y < TYN; ++y) sum += red[(y * TXN + txp) * V + v];
+            const int c = txp + TXN * i;
+            int dst;
+            if (s < A) dst = L.off_w3() + s * H + c;
+            else if (s == A) dst = L.off_b2() + c;
+            else if (s <= A + O) dst = L.off_w1() + c * O + (s - A - 1);
+            else dst = L.off_b1() + c;
+            out[dst] = sum;
+        }
+        __syncthreads();
+    }
+    // row-owned scalars (threads 0..R-1): db3, dlog_std, statistics
+    {
+        constexpr int NS = A + 1 + 5;
+        float vals[NS];
+#pragma unroll
+        for (int q = 0; q < A; ++q) vals[q] = gB3[q];
+        vals[A] = gLs; vals[A + 1] = st_loss; vals[A + 2] = st_kl; vals[A + 3] = st_ent;
+        vals[A + 4] = st_clip; vals[A + 5] = st_rows;
+#pragma unroll
+        for (int s = 0; s < NS; ++s) {
+            float v = vals[s];
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) v += __shfl_down_sync(0xffffffffu, v, o);
+            if (l == 0) red[s * 8 + w] = v;
+        }
+        __syncthreads();
+        if (tid < NS) {
+            float sum = 0.0f;
+            for (int y = 0; y < MLP_NT / 32; ++y) sum += red[tid * 8 + y];
+            if (tid < A) { if (BWD) out[L.off_b3() + tid] = sum; }
+            else if (tid == A) { if (BWD) out[L.off_logstd()] = sum; }
+            else out[P + (tid - A - 1)] = sum;
+        }
+        if (tid >= NS && tid < NS + (MLP_NSTATS - 5)) out[P + 5 + (tid - NS)] = 0.0f;
+    }
+}
+
+template <int H, int O, int A, bool BWD>
+constexpr size_t mlp_train_smem_bytes() {
+    return sizeof(float) * (size_t)(O * MLP_RS + 2 * H * MLP_RS + A * MLP_RS + H * H +
+                                    (BWD ? H * H : 0) + H * O + 2 * H + A * H + 4);
+}

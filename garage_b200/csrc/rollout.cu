@@ -280,3 +280,43 @@ extern "C" int b2g_rollout(int env_id, const double* params, int max_episode_len
 extern "C" int64_t b2g_mlp_param_count(int obs_dim, int hidden, int out_dim) {
     return MlpLayout{obs_dim, hidden, out_dim}.total();
 }
+
+// ---- stand-alone sampling for StochasticPolicy.get_actions
+// (torch/policies/stochastic_policy.py:46-89: dist.sample() and agent_info), same
+// Philox stream as the rollout kernel: action = mean + std * eps(gid0 + i, t_counter).
+template <int A>
+__global__ void __launch_bounds__(128)
+policy_sample_kernel(const float* __restrict__ mean, float log_std, uint32_t seed_lo,
+                     uint32_t seed_hi, int64_t gid0, uint32_t t_counter,
+                     float* __restrict__ act, float* __restrict__ logp, int64_t n) {
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const float stdv = expf(log_std), var = stdv * stdv, log_scale = logf(stdv);
+    float eps[A];
+    action_noise<A>(seed_lo, seed_hi, (uint32_t)(gid0 + i), t_counter, eps);
+    float lp = 0.0f;
+#pragma unroll
+    for (int q = 0; q < A; ++q) {
+        const float mu = mean[i * A + q];
+        const float av = fmaf(stdv, eps[q], mu);
+        act[i * A + q] = av;
+        lp += normal_logp_term(av, mu, var, log_scale);
+    }
+    if (logp) logp[i] = lp;
+}
+
+extern "C" int b2g_policy_sample(const float* mean, int act_dim, float log_std, uint64_t seed,
+                                 int64_t env_id_offset, uint32_t t_counter, float* act_out,
+                                 float* logp_out, int64_t n, void* stream) {
+    B2G_CHECK_ARG(n >= 0, "negative n");
+    if (n == 0) return B2G_OK;
+    B2G_CHECK_ARG(mean && act_out, "NULL pointer");
+    const unsigned blocks = (unsigned)((n + 127) / 128);
+    cudaStream_t s = (cudaStream_t)stream;
+    const uint32_t lo = (uint32_t)seed, hi = (uint32_t)(seed >> 32);
+    if (act_dim == 1) policy_sample_kernel<1><<<blocks, 128, 0, s>>>(mean, log_std, lo, hi, env_id_offset, t_counter, act_out, logp_out, n);
+    else if (act_dim == 2) policy_sample_kernel<2><<<blocks, 128, 0, s>>>(mean, log_std, lo, hi, env_id_offset, t_counter, act_out, logp_out, n);
+    else { b2g_set_error("b2g_policy_sample: act_dim %d not built (1 or 2)", act_dim); return B2G_ERR_UNSUPPORTED; }
+    B2G_CHECK_LAUNCH();
+    return B2G_OK;
+}

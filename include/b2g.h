@@ -210,6 +210,82 @@ int b2g_pack_fields(const uint8_t* step_type, const int32_t* ep_len, const int64
                     int T_used, int64_t N, int n_fields, const void* const* src,
                     void* const* dst, const int* bytes_per_step, void* stream);
 
+/* StochasticPolicy.get_actions sampling (torch/policies/stochastic_policy.py:46-89):
+ * act = mean + exp(log_std) * eps, eps = Philox(seed; env_id_offset + i, t_counter),
+ * logp_out[n] (may be NULL) = Independent(Normal).log_prob(act).  log_std is the
+ * already clamped scalar. */
+int b2g_policy_sample(const float* mean, int act_dim, float log_std, uint64_t seed,
+                      int64_t env_id_offset, uint32_t t_counter, float* act_out,
+                      float* logp_out, int64_t n, void* stream);
+
+/* ------------------------------------------------- minibatch MLP update --
+ * Fused gather -> MLP forward -> loss -> backward for ONE minibatch of garage's
+ * GaussianMLPPolicy / GaussianMLPValueFunction (parameter vector as above).
+ *   replaces torch/algos/vpg.py:250-293 (_train_policy/_train_value_function:
+ *   zero_grad, loss, backward), torch/algos/ppo.py:96-132 (clipped surrogate),
+ *   vpg.py:324-347,408-455 (loss/entropy/VPG objective),
+ *   value_functions/gaussian_mlp_value_function.py:81-97 (Gaussian NLL) and the
+ *   autograd graph of torch/modules/multi_headed_mlp_module.py:136-151.
+ *   rows: idx[mb] (int32 row ids into the flat [B,...] arrays, the reference's
+ *   BatchDataset ids, np/optimizers/minibatch_dataset.py:21-35) or, with
+ *   idx == NULL, rows start..start+mb.
+ *   loss_kind: 0 PPO (needs act, adv, old_logp), 1 VPG (act, adv), 2 value NLL
+ *   (ret; out_dim 1), [3 none: forward only, b2g_mlp_eval].
+ *   flags: 1 entropy regularised, 2 softplus entropy, 4 stop entropy gradient.
+ *   Result: ws_partial[n_partials][P + 8] per-CTA sums of UNSCALED gradients
+ *   (d sum_rows loss_row) and statistics [sum loss_row, sum KL, sum entropy,
+ *   #rows outside the clip range, #rows, 0,0,0]; n_partials =
+ *   b2g_mlp_num_partials(obs_dim, hidden, out_dim, 1, mb); ws_partial holds at
+ *   least b2g_mlp_ws_floats() floats.  step_counter (device u64, may be NULL)
+ *   is incremented once per call: it is the Adam step of b2g_mlp_reduce /
+ *   b2g_adam_step launched after it on the same stream (graph-capturable).
+ */
+#define B2G_LOSS_PPO 0
+#define B2G_LOSS_VPG 1
+#define B2G_LOSS_VF 2
+#define B2G_LOSS_NONE 3
+#define B2G_FLAG_ENT_REG 1
+#define B2G_FLAG_SOFTPLUS_ENT 2
+#define B2G_FLAG_STOP_ENT_GRAD 4
+#define B2G_MLP_NSTATS 8
+
+int b2g_mlp_num_partials(int obs_dim, int hidden, int out_dim, int backward, int64_t rows);
+int64_t b2g_mlp_ws_floats(int obs_dim, int hidden, int out_dim);
+
+int b2g_mlp_minibatch_grad(int obs_dim, int hidden, int out_dim, const float* params,
+                           const int32_t* idx, int64_t start, int64_t mb, const float* obs,
+                           const float* act, const float* adv, const float* old_logp,
+                           const float* ret, int loss_kind, int flags, float clip,
+                           float ent_coeff, float min_log_std, float max_log_std,
+                           float* ws_partial, unsigned long long* step_counter, void* stream);
+
+/* Forward only over n rows: mean_out[n,out_dim] (may be NULL; policy means /
+ * value baselines, vpg.py:155-156) and the same statistics as above, plus
+ * sum KL(old || new) when old_mean[B,out_dim] is given (vpg.py:381-406, the old
+ * policy is the rollout policy, Q8).  n_partials =
+ * b2g_mlp_num_partials(..., 0, n). */
+int b2g_mlp_eval(int obs_dim, int hidden, int out_dim, const float* params, const int32_t* idx,
+                 int64_t start, int64_t n, const float* obs, const float* act, const float* adv,
+                 const float* old_logp, const float* ret, const float* old_mean,
+                 float old_log_std, int loss_kind, int flags, float clip, float ent_coeff,
+                 float min_log_std, float max_log_std, float* mean_out, float* ws_partial,
+                 void* stream);
+
+/* Reduce the per-CTA partials in fixed order: grad_out[n_params] (may be NULL) =
+ * scale * sum; stats_out (device double[8], may be NULL) = sums.  With params
+ * != NULL also applies torch.optim.Adam's update (make_optimizer,
+ * _functions.py:25-65; amsgrad False, weight_decay 0) in place, step =
+ * *step_counter. */
+int b2g_mlp_reduce(const float* ws_partial, int n_partials, int n_params, float scale,
+                   float* grad_out, double* stats_out, float* params, float* adam_m,
+                   float* adam_v, const unsigned long long* step_counter, double lr,
+                   double beta1, double beta2, double eps, void* stream);
+
+/* Adam on a gradient vector that was all-reduced across ranks (grad * grad_scale). */
+int b2g_adam_step(float* params, const float* grad, float grad_scale, float* adam_m,
+                  float* adam_v, const unsigned long long* step_counter, double lr, double beta1,
+                  double beta2, double eps, int n, void* stream);
+
 #ifdef __cplusplus
 }
 #endif
