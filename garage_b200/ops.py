@@ -111,3 +111,253 @@ def normalize_adv(x, stats, center_adv=True, positive_adv=False, out=None):
         call('b2g_normalize_adv', ptr(x), ptr(stats), int(bool(center_adv)), int(bool(positive_adv)),
              ptr(out), int(x.numel()), _stream(x))
     return out
+
+
+# ------------------------------------------------------------------ envs --
+import ctypes  # noqa: E402
+import math  # noqa: E402
+
+ENV_POINT, ENV_PENDULUM, ENV_CARTPOLE = 0, 1, 2
+ENV_NPARAMS = 10
+
+
+def env_params_array(values):
+    arr = (ctypes.c_double * ENV_NPARAMS)()
+    for i, v in enumerate(values):
+        arr[i] = float(v)
+    return arr
+
+
+def env_dims(env_id):
+    lib = _lib.load()
+    return lib.b2g_env_obs_dim(env_id), lib.b2g_env_act_dim(env_id), lib.b2g_env_state_dim(env_id)
+
+
+class EnvState:
+    """Device-resident state of N batched environments (caller-owned tensors)."""
+
+    def __init__(self, env_id, n, device):
+        O, A, S = env_dims(env_id)
+        self.env_id, self.n, self.device = env_id, n, device
+        self.state = torch.zeros(S, n, dtype=torch.float64, device=device)
+        self.obs = torch.zeros(n, O, dtype=torch.float32, device=device)
+        self.step_cnt = torch.full((n, ), -1, dtype=torch.int32, device=device)
+        self.episode = torch.zeros(n, dtype=torch.int32, device=device)
+
+
+def env_reset(es, params, seed, env_id_offset=0):
+    with torch.cuda.device(es.device):
+        call('b2g_env_reset', es.env_id, params, int(seed) & (2**64 - 1), int(env_id_offset),
+             ptr(es.state), ptr(es.obs), ptr(es.step_cnt), ptr(es.episode), es.n, _stream(es.state))
+
+
+def env_step(es, params, max_episode_length, actions, want_success=False):
+    """One Environment.step() for all envs. Returns (obs, reward f64, step_type u8, success|None)."""
+    _chk(actions, torch.float32, 'actions')
+    O, A, S = env_dims(es.env_id)
+    if actions.shape != (es.n, A):
+        raise ValueError('actions must be [{}, {}]'.format(es.n, A))
+    dev = es.device
+    obs = torch.empty(es.n, O, dtype=torch.float32, device=dev)
+    rew = torch.empty(es.n, dtype=torch.float64, device=dev)
+    st = torch.empty(es.n, dtype=torch.uint8, device=dev)
+    succ = torch.empty(es.n, dtype=torch.uint8, device=dev) if want_success else None
+    err = torch.zeros(1, dtype=torch.int32, device=dev)
+    with torch.cuda.device(dev):
+        call('b2g_env_step', es.env_id, params, int(max_episode_length or 0), ptr(es.state),
+             ptr(actions), ptr(obs), ptr(rew), ptr(st), ptr(succ), ptr(es.step_cnt), ptr(err),
+             es.n, _stream(actions))
+    bad = int(err.item())
+    if bad:
+        # the reference raises RuntimeError (envs/point_env.py:113-114)
+        raise RuntimeError('reset() must be called before step()! (env {})'.format(bad - 1))
+    es.obs = obs
+    return obs, rew, st, succ
+
+
+# --------------------------------------------------------------- rollout --
+def mlp_param_count(obs_dim, hidden, out_dim):
+    return int(_lib.load().b2g_mlp_param_count(obs_dim, hidden, out_dim))
+
+
+class RolloutBuffers:
+    """Time-major [T,N,...] rollout buffers (caller-owned)."""
+
+    def __init__(self, env_id, T, n, device, want_mean=True, want_success=False):
+        O, A, S = env_dims(env_id)
+        f32 = dict(dtype=torch.float32, device=device)
+        self.T, self.n = T, n
+        self.obs = torch.empty(T, n, O, **f32)
+        self.act = torch.empty(T, n, A, **f32)
+        self.rew = torch.empty(T, n, **f32)
+        self.logp = torch.empty(T, n, **f32)
+        self.step_type = torch.empty(T, n, dtype=torch.uint8, device=device)
+        self.mean = torch.empty(T, n, A, **f32) if want_mean else None
+        self.success = torch.empty(T, n, dtype=torch.uint8, device=device) if want_success else None
+        self.last_obs = torch.empty(T, n, O, **f32)
+        self.ep_len = torch.empty(T, n, dtype=torch.int32, device=device)
+
+
+def rollout(es, params, max_episode_length, policy_flat, hidden, min_log_std, max_log_std, seed,
+            env_id_offset, t_counter, buf, t0, n_steps):
+    """b2g_rollout for rows t0..t0+n_steps of `buf`."""
+    _chk(policy_flat, torch.float32, 'policy_flat')
+    if t0 + n_steps > buf.T:
+        raise ValueError('rollout rows exceed the buffer')
+
+    def row(t):
+        return None if t is None else t[t0:]
+
+    with torch.cuda.device(es.device):
+        call('b2g_rollout', es.env_id, params, int(max_episode_length or 0), ptr(policy_flat),
+             int(hidden), float(min_log_std), float(max_log_std), int(seed) & (2**64 - 1),
+             int(env_id_offset), int(t_counter) & 0xffffffff, ptr(es.state), ptr(es.obs),
+             ptr(es.step_cnt), ptr(es.episode), int(n_steps), es.n, ptr(row(buf.obs)),
+             ptr(row(buf.act)), ptr(row(buf.rew)), ptr(row(buf.logp)), ptr(row(buf.step_type)),
+             ptr(row(buf.mean)), ptr(row(buf.success)), ptr(row(buf.last_obs)),
+             ptr(row(buf.ep_len)), _stream(policy_flat))
+
+
+def policy_sample(mean, log_std, seed, env_id_offset, t_counter, want_logp=True):
+    _chk(mean, torch.float32, 'mean')
+    n, A = mean.shape
+    act = torch.empty_like(mean)
+    logp = torch.empty(n, dtype=torch.float32, device=mean.device) if want_logp else None
+    with torch.cuda.device(mean.device):
+        call('b2g_policy_sample', ptr(mean), int(A), float(log_std), int(seed) & (2**64 - 1),
+             int(env_id_offset), int(t_counter) & 0xffffffff, ptr(act), ptr(logp), int(n),
+             _stream(mean))
+    return act, logp
+
+
+# ------------------------------------------------------------------ pack --
+def pack_plan(step_type, ep_len, T, num_samples):
+    """Returns (ws, (t_star, n_eps, n_steps, reached)) -- one small D2H sync."""
+    _chk(step_type, torch.uint8, 'step_type')
+    _chk(ep_len, torch.int32, 'ep_len')
+    N = step_type.shape[1]
+    dev = step_type.device
+    ws = torch.empty(int(_lib.load().b2g_pack_ws_bytes(T)), dtype=torch.uint8, device=dev)
+    summary = torch.empty(4, dtype=torch.int64, device=dev)
+    with torch.cuda.device(dev):
+        call('b2g_pack_plan', ptr(step_type), ptr(ep_len), int(T), int(N), int(num_samples), ptr(ws),
+             ptr(summary), _stream(step_type))
+    t_star, n_eps, n_steps, reached = (int(v) for v in summary.tolist())
+    return ws, (t_star, n_eps, n_steps, bool(reached))
+
+
+def pack_index(step_type, ep_len, last_obs, ws, T_ws, t_star, n_eps):
+    N = step_type.shape[1]
+    dev = step_type.device
+    O = last_obs.shape[-1]
+    lengths = torch.empty(n_eps, dtype=torch.int64, device=dev)
+    ep_off = torch.empty(t_star + 1, N, dtype=torch.int64, device=dev)
+    last_observations = torch.empty(n_eps, O, dtype=torch.float32, device=dev)
+    ep_env = torch.empty(n_eps, dtype=torch.int32, device=dev)
+    ep_end = torch.empty(n_eps, dtype=torch.int32, device=dev)
+    with torch.cuda.device(dev):
+        call('b2g_pack_index', ptr(step_type), ptr(ep_len), ptr(last_obs), int(O), int(t_star + 1),
+             int(T_ws), int(N), ptr(ws), ptr(lengths), ptr(ep_off), ptr(last_observations),
+             ptr(ep_env), ptr(ep_end), _stream(step_type))
+    return lengths, ep_off, last_observations, ep_env, ep_end
+
+
+def pack_fields(step_type, ep_len, ep_off, t_star, n_steps, fields):
+    """fields: list of time-major tensors [T,N,...]; returns packed [n_steps,...] tensors."""
+    N = step_type.shape[1]
+    dev = step_type.device
+    outs = []
+    for f in fields:
+        if not f.is_contiguous() or not f.is_cuda:
+            raise ValueError('pack fields must be contiguous CUDA tensors')
+        outs.append(torch.empty((n_steps, ) + tuple(f.shape[2:]), dtype=f.dtype, device=dev))
+    for i in range(0, len(fields), 12):
+        fs, os_ = fields[i:i + 12], outs[i:i + 12]
+        k = len(fs)
+        src = (ctypes.c_void_p * k)(*[f.data_ptr() for f in fs])
+        dst = (ctypes.c_void_p * k)(*[o.data_ptr() for o in os_])
+        nbytes = (ctypes.c_int * k)(*[f.element_size() * int(math.prod(f.shape[2:])) for f in fs])
+        with torch.cuda.device(dev):
+            call('b2g_pack_fields', ptr(step_type), ptr(ep_len), ptr(ep_off), int(t_star + 1), int(N),
+                 k, src, dst, nbytes, _stream(step_type))
+    return outs
+
+
+# ------------------------------------------------------------- MLP update --
+LOSS_PPO, LOSS_VPG, LOSS_VF, LOSS_NONE = 0, 1, 2, 3
+FLAG_ENT_REG, FLAG_SOFTPLUS_ENT, FLAG_STOP_ENT_GRAD = 1, 2, 4
+MLP_NSTATS = 8
+INF = float('inf')
+
+
+class MlpShape:
+    """(obs_dim, hidden, out_dim) of a two-hidden-layer Gaussian MLP + its workspace."""
+
+    def __init__(self, obs_dim, hidden, out_dim, device):
+        self.O, self.H, self.A = int(obs_dim), int(hidden), int(out_dim)
+        lib = _lib.load()
+        if lib.b2g_mlp_num_partials(self.O, self.H, self.A, 1, 1) < 0:
+            raise NotImplementedError(lib.b2g_last_error().decode())
+        self.P = int(lib.b2g_mlp_param_count(self.O, self.H, self.A))
+        self.device = device
+        self.ws = torch.empty(int(lib.b2g_mlp_ws_floats(self.O, self.H, self.A)),
+                              dtype=torch.float32, device=device)
+
+    def num_partials(self, backward, rows):
+        return int(_lib.load().b2g_mlp_num_partials(self.O, self.H, self.A, int(backward), int(rows)))
+
+
+def mlp_minibatch_grad(shape, params, obs, *, idx=None, start=0, mb=None, act=None, adv=None,
+                       old_logp=None, ret=None, loss_kind, flags=0, clip=0.2, ent_coeff=0.0,
+                       min_log_std=-INF, max_log_std=INF, step_counter=None):
+    """Launch the fused fwd/loss/bwd kernel for one minibatch; partials land in shape.ws."""
+    _chk(params, torch.float32, 'params')
+    _chk(obs, torch.float32, 'obs')
+    _chk(idx, torch.int32, 'idx')
+    for name, t in (('act', act), ('adv', adv), ('old_logp', old_logp), ('ret', ret)):
+        _chk(t, torch.float32, name)
+    if params.numel() != shape.P:
+        raise ValueError('params has {} elements, expected {}'.format(params.numel(), shape.P))
+    if mb is None:
+        mb = idx.numel() if idx is not None else obs.shape[0] - start
+    with torch.cuda.device(shape.device):
+        call('b2g_mlp_minibatch_grad', shape.O, shape.H, shape.A, ptr(params), ptr(idx), int(start),
+             int(mb), ptr(obs), ptr(act), ptr(adv), ptr(old_logp), ptr(ret), int(loss_kind),
+             int(flags), float(clip), float(ent_coeff), float(min_log_std), float(max_log_std),
+             ptr(shape.ws), ptr(step_counter), _stream(params))
+    return shape.num_partials(True, mb)
+
+
+def mlp_eval(shape, params, obs, *, idx=None, start=0, n=None, act=None, adv=None, old_logp=None,
+             ret=None, old_mean=None, old_log_std=0.0, loss_kind=LOSS_NONE, flags=0, clip=0.2,
+             ent_coeff=0.0, min_log_std=-INF, max_log_std=INF, mean_out=None):
+    _chk(params, torch.float32, 'params')
+    _chk(obs, torch.float32, 'obs')
+    _chk(idx, torch.int32, 'idx')
+    _chk(mean_out, torch.float32, 'mean_out')
+    if n is None:
+        n = idx.numel() if idx is not None else obs.shape[0] - start
+    with torch.cuda.device(shape.device):
+        call('b2g_mlp_eval', shape.O, shape.H, shape.A, ptr(params), ptr(idx), int(start), int(n),
+             ptr(obs), ptr(act), ptr(adv), ptr(old_logp), ptr(ret), ptr(old_mean),
+             float(old_log_std), int(loss_kind), int(flags), float(clip), float(ent_coeff),
+             float(min_log_std), float(max_log_std), ptr(mean_out), ptr(shape.ws), _stream(params))
+    return shape.num_partials(False, n)
+
+
+def mlp_reduce(shape, n_partials, scale, *, grad_out=None, stats_out=None, params=None, adam_m=None,
+               adam_v=None, step_counter=None, lr=0.0, beta1=0.9, beta2=0.999, eps=1e-8):
+    _chk(grad_out, torch.float32, 'grad_out')
+    _chk(stats_out, torch.float64, 'stats_out')
+    with torch.cuda.device(shape.device):
+        call('b2g_mlp_reduce', ptr(shape.ws), int(n_partials), shape.P, float(scale), ptr(grad_out),
+             ptr(stats_out), ptr(params), ptr(adam_m), ptr(adam_v), ptr(step_counter), float(lr),
+             float(beta1), float(beta2), float(eps), _stream(shape.ws))
+
+
+def adam_step(params, grad, grad_scale, adam_m, adam_v, step_counter, lr, beta1=0.9, beta2=0.999,
+              eps=1e-8):
+    with torch.cuda.device(params.device):
+        call('b2g_adam_step', ptr(params), ptr(grad), float(grad_scale), ptr(adam_m), ptr(adam_v),
+             ptr(step_counter), float(lr), float(beta1), float(beta2), float(eps),
+             int(params.numel()), _stream(params))

@@ -287,3 +287,251 @@ def cartpole_step(state, action, gravity=9.8, masscart=1.0, masspole=0.1, length
     new_state = np.stack([x, x_dot, theta, theta_dot], axis=1)
     done = (x < -x_threshold) | (x > x_threshold) | (theta < -theta_threshold) | (theta > theta_threshold)
     return new_state, new_state.astype(np.float32), np.ones(x.shape, np.float64), done
+
+
+# ------------------------------------------------- Gaussian MLP (policy / VF) --
+LOG_SQRT_2PI = math.log(math.sqrt(2 * math.pi))
+
+
+def mlp_param_count(O, H, A):
+    return 1 + H * O + H + H * H + H + A * H + A
+
+
+def unflatten_params(flat, O, H, A):
+    """garage_b200's flat layout == GaussianMLPPolicy.state_dict() order
+    (torch/policies/gaussian_mlp_policy.py:53-87, hidden_sizes=(H,H)):
+    [log_std | W1[H,O] | b1[H] | W2[H,H] | b2[H] | W3[A,H] | b3[A]]."""
+    flat = np.asarray(flat)
+    i = 0
+    out = {}
+    for name, shape in (('log_std', (1, )), ('W1', (H, O)), ('b1', (H, )), ('W2', (H, H)),
+                        ('b2', (H, )), ('W3', (A, H)), ('b3', (A, ))):
+        n = int(np.prod(shape))
+        out[name] = flat[i:i + n].reshape(shape)
+        i += n
+    assert i == flat.shape[0]
+    return out
+
+
+def flatten_params(p):
+    return np.concatenate([np.asarray(p[k]).ravel() for k in ('log_std', 'W1', 'b1', 'W2', 'b2', 'W3', 'b3')])
+
+
+def mlp_forward(p, obs, dtype=np.float64):
+    """torch/modules/multi_headed_mlp_module.py:136-151 with tanh hidden layers
+    (gaussian_mlp_policy.py:56): returns (mean, h1, h2)."""
+    x = np.asarray(obs, dtype)
+    h1 = np.tanh(x @ p['W1'].astype(dtype).T + p['b1'].astype(dtype))
+    h2 = np.tanh(h1 @ p['W2'].astype(dtype).T + p['b2'].astype(dtype))
+    mean = h2 @ p['W3'].astype(dtype).T + p['b3'].astype(dtype)
+    return mean, h1, h2
+
+
+def clamped_log_std(p, min_std=1e-6, max_std=None):
+    """gaussian_mlp_module.py:171-176 (clamp only; returns (log_std, grad passes))."""
+    ls = float(p['log_std'][0])
+    lo = -np.inf if min_std is None else float(np.float32(np.log(np.float32(min_std))))
+    hi = np.inf if max_std is None else float(np.float32(np.log(np.float32(max_std))))
+    return min(max(ls, lo), hi), (lo <= ls <= hi)
+
+
+def normal_log_prob(x, mean, log_std):
+    """Independent(Normal(mean, exp(log_std)), 1).log_prob(x), torch.distributions.normal."""
+    var = math.exp(log_std)**2
+    return (-((x - mean)**2) / (2 * var) - log_std - LOG_SQRT_2PI).sum(-1)
+
+
+def normal_entropy(log_std, act_dim):
+    return act_dim * (0.5 + 0.5 * math.log(2 * math.pi) + log_std)
+
+
+def kl_normal(mean_p, log_std_p, mean_q, log_std_q):
+    """torch.distributions.kl._kl_normal_normal summed over action dims (Independent)."""
+    vr = (math.exp(log_std_p) / math.exp(log_std_q))**2
+    t1 = ((mean_p - mean_q) / math.exp(log_std_q))**2
+    return (0.5 * (vr + t1 - 1 - math.log(vr))).sum(-1)
+
+
+def policy_loss_and_grad(flat, O, H, A, obs, act, adv, old_logp, kind='ppo', clip=0.2,
+                         min_std=1e-6, max_std=None, ent_coeff=0.0, entropy_regularized=False,
+                         use_softplus_entropy=False, stop_entropy_gradient=False):
+    """loss = -mean(objective) and d loss / d flat, in float64.
+    PPO objective: torch/algos/ppo.py:96-132; VPG: vpg.py:434-455; entropy term:
+    vpg.py:324-347, 408-432.  Backward written out by hand (tanh MLP, nn.Linear)."""
+    p = unflatten_params(np.asarray(flat, np.float64), O, H, A)
+    obs = np.asarray(obs, np.float64)
+    act = np.asarray(act, np.float64)
+    adv = np.asarray(adv, np.float64)
+    n = obs.shape[0]
+    mean, h1, h2 = mlp_forward(p, obs)
+    ls, ls_pass = clamped_log_std(p, min_std, max_std)
+    var = math.exp(ls)**2
+    ll = normal_log_prob(act, mean, ls)
+    if kind == 'ppo':
+        ratio = np.exp(ll - np.asarray(old_logp, np.float64))
+        surr = ratio * adv
+        rc = np.clip(ratio, 1 - clip, 1 + clip)
+        surr_c = rc * adv
+        obj = np.minimum(surr, surr_c)
+        inside = (ratio >= 1 - clip) & (ratio <= 1 + clip)
+        dobj_dll = np.where(inside | (surr < surr_c), ratio * adv, 0.0)
+    else:
+        obj = ll * adv
+        dobj_dll = adv.copy()
+    dobj_dls_ent = 0.0
+    if entropy_regularized:
+        ent = normal_entropy(ls, A)
+        dent = float(A)
+        if use_softplus_entropy:
+            dent *= 1.0 / (1.0 + math.exp(-ent))
+            ent = math.log1p(math.exp(ent))
+        obj = obj + ent_coeff * ent
+        if not stop_entropy_gradient:
+            dobj_dls_ent = ent_coeff * dent
+    loss = -obj.mean()
+    d = act - mean
+    dmean = -(dobj_dll[:, None] * d / var) / n
+    dls = (-(dobj_dll * ((d**2).sum(-1) / var - A)).sum() / n - dobj_dls_ent) if ls_pass else 0.0
+    return loss, _mlp_backward(p, obs, h1, h2, dmean, dls)
+
+
+def vf_loss_and_grad(flat, O, H, obs, ret):
+    """value_functions/gaussian_mlp_value_function.py:81-97: -mean log N(ret; V(obs), exp(s));
+    min_std=None -> no clamp (:76-77)."""
+    p = unflatten_params(np.asarray(flat, np.float64), O, H, 1)
+    obs = np.asarray(obs, np.float64)
+    ret = np.asarray(ret, np.float64).reshape(-1, 1)
+    n = obs.shape[0]
+    mean, h1, h2 = mlp_forward(p, obs)
+    ls = float(p['log_std'][0])
+    var = math.exp(ls)**2
+    loss = -normal_log_prob(ret, mean, ls).mean()
+    d = ret - mean
+    dmean = -(d / var) / n
+    dls = (1.0 - (d**2).sum(-1) / var).sum() / n
+    return loss, _mlp_backward(p, obs, h1, h2, dmean, dls)
+
+
+def _mlp_backward(p, obs, h1, h2, dmean, dls):
+    g = {}
+    g['log_std'] = np.array([dls])
+    g['W3'] = dmean.T @ h2
+    g['b3'] = dmean.sum(0)
+    dz2 = (dmean @ p['W3']) * (1 - h2**2)
+    g['W2'] = dz2.T @ h1
+    g['b2'] = dz2.sum(0)
+    dz1 = (dz2 @ p['W2']) * (1 - h1**2)
+    g['W1'] = dz1.T @ obs
+    g['b1'] = dz1.sum(0)
+    return flatten_params(g)
+
+
+def adam_step(param, grad, m, v, step, lr=2.5e-4, beta1=0.9, beta2=0.999, eps=1e-8):
+    """torch.optim.Adam single-tensor update (amsgrad=False, weight_decay=0), float32
+    state like the reference's CPU tensors; step counts from 1."""
+    f = np.float32
+    param, grad, m, v = (np.asarray(a, f) for a in (param, grad, m, v))
+    m = (m + f(1 - beta1) * (grad - m)).astype(f)
+    v = (v * f(beta2) + (f(1 - beta2) * grad) * grad).astype(f)
+    bc1 = 1 - beta1**step
+    bc2 = 1 - beta2**step
+    step_size = f(lr / bc1)
+    denom = (np.sqrt(v) / f(math.sqrt(bc2)) + f(eps)).astype(f)
+    param = (param - step_size * (m / denom)).astype(f)
+    return param, m, v
+
+
+# ------------------------------------------------ vectorised rollout replay --
+def env_reset_states(env, seed, gid, episode, goal=(1., 1.)):
+    """Initial (state, obs) of `episode` of each global env id: PointEnv resets to
+    the origin (point_env.py:79-98); Pendulum/CartPole draw U(-high, high) like gym
+    0.17.2's reset() but from garage_b200's Philox reset stream."""
+    n = len(gid)
+    if env == 'point':
+        return point_reset(n, goal)
+    if env == 'pendulum':
+        u0, u1 = reset_uniforms(seed, gid, episode, 0)
+        st = np.stack([(2 * u0 - 1) * np.pi, (2 * u1 - 1) * 1.0], axis=1)
+        return st, pendulum_obs(st)
+    u0, u1 = reset_uniforms(seed, gid, episode, 0)
+    u2, u3 = reset_uniforms(seed, gid, episode, 1)
+    st = np.stack([(2 * u - 1) * 0.05 for u in (u0, u1, u2, u3)], axis=1)
+    return st, st.astype(np.float32)
+
+
+def env_step_any(env, state, action, kw):
+    if env == 'point':
+        p, obs, rew, done, succ = point_step(state, action, **kw)
+        return p, obs, rew, done, succ
+    if env == 'pendulum':
+        s, obs, rew, done = pendulum_step(state, action, **kw)
+    else:
+        s, obs, rew, done = cartpole_step(state, action, **kw)
+    return s, obs, rew, done, np.zeros(done.shape, bool)
+
+
+def replay_rollout(env, actions, max_episode_length, seed, gid0=0, first_episode=0, env_kw=None):
+    """Replay recorded actions [T,N,A] through N vectorised envs with the
+    bookkeeping of sampler/vec_worker.py:176-204: per-env step counters,
+    StepType.get_step_type (_dtypes.py:44-68), last observation kept at the
+    finishing step (Q10), immediate reset of a finished env (:171)."""
+    env_kw = dict(env_kw or {})
+    actions = np.asarray(actions, np.float32)
+    T, N, A = actions.shape
+    gid = np.arange(gid0, gid0 + N)
+    ep = np.full(N, first_episode, np.int64)
+    goal = env_kw.get('goal', (1., 1.))
+    state, obs = env_reset_states(env, seed, gid, ep, goal)
+    ep += 1
+    O_ = obs.shape[1]
+    out = dict(obs=np.zeros((T, N, O_), np.float32), rew=np.zeros((T, N), np.float64),
+               step_type=np.zeros((T, N), np.uint8), success=np.zeros((T, N), bool),
+               last_obs=np.zeros((T, N, O_), np.float32), ep_len=np.zeros((T, N), np.int32))
+    cnt = np.zeros(N, np.int64)
+    for t in range(T):
+        out['obs'][t] = obs
+        state, obs, rew, done, succ = env_step_any(env, state, actions[t], env_kw)
+        cnt += 1
+        st = np.where(cnt == 1, FIRST, MID)
+        st = np.where(done, TERMINAL, st)
+        if max_episode_length:
+            st = np.where(cnt >= max_episode_length, TIMEOUT, st)
+        out['rew'][t] = rew
+        out['step_type'][t] = st
+        out['success'][t] = succ
+        last = st >= TERMINAL
+        if last.any():
+            out['last_obs'][t][last] = obs[last]
+            out['ep_len'][t][last] = cnt[last]
+            rs, ro = env_reset_states(env, seed, gid[last], ep[last], goal)
+            state = np.array(state)
+            obs = np.array(obs)
+            state[last] = rs
+            obs[last] = ro
+            ep[last] += 1
+            cnt[last] = 0
+    return out
+
+
+def pack_episodes(step_type, ep_len, num_samples, fields):
+    """Episode-major packing with the reference's ordering and cut:
+    episodes in completion order, ties by env index (vec_worker.py:185-201 loops
+    envs in index order inside a step), stop after the first step at which
+    completed samples >= num_samples (local_sampler.py:156-166).
+    Returns (lengths, [packed fields], [(t_end, n)])."""
+    T, N = step_type.shape
+    eps = []
+    total = 0
+    for t in range(T):
+        row = np.nonzero(step_type[t] >= TERMINAL)[0]
+        for n in row:
+            eps.append((t, int(n), int(ep_len[t, n])))
+            total += int(ep_len[t, n])
+        if total >= num_samples:
+            break
+    lengths = np.array([L for _, _, L in eps], dtype=np.int64)
+    packed = []
+    for f in fields:
+        parts = [f[t - L + 1:t + 1, n] for t, n, L in eps]
+        packed.append(np.concatenate(parts) if parts else f[:0, 0])
+    return lengths, packed, [(t, n) for t, n, _ in eps]
