@@ -124,7 +124,7 @@ def test_rollout_replay_parity(name, H, N, T, max_len):
     done = ref['step_type'] >= O.TERMINAL
     assert np.array_equal(g['ep_len'][done], ref['ep_len'][done])           # bit-exact
     assert np.array_equal(g['success'].astype(bool), ref['success'])        # bit-exact
-    assert done.any()
+    assert done.any() or T < max_len
     assert np.allclose(g['obs'], ref['obs'], rtol=1e-5, atol=1e-6)
     assert np.allclose(g['rew'], ref['rew'], rtol=1e-5, atol=1e-6)
     assert np.allclose(g['last_obs'][done], ref['last_obs'][done], rtol=1e-5, atol=1e-6)
