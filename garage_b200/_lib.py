@@ -27,14 +27,16 @@ SIGNATURES = {
     'b2g_moments_ws_bytes': (c_int64, []),
     'b2g_moments': (c_int, [P, c_int64, P, P, P]),
     'b2g_normalize_adv': (c_int, [P, P, c_int, c_int, P, c_int64, P]),
+    'b2g_permutation': (c_int, [c_uint64, P, c_uint64, c_int64, P, P]),
     'b2g_env_obs_dim': (c_int, [c_int]),
     'b2g_env_act_dim': (c_int, [c_int]),
     'b2g_env_state_dim': (c_int, [c_int]),
     'b2g_env_reset': (c_int, [c_int, POINTER(c_double), c_uint64, c_int64, P, P, P, P, c_int64, P]),
     'b2g_env_step': (c_int, [c_int, POINTER(c_double), c_int, P, P, P, P, P, P, P, P, c_int64, P]),
     'b2g_mlp_param_count': (c_int64, [c_int, c_int, c_int]),
+    'b2g_counter_add': (c_int, [P, c_uint64, P]),
     'b2g_rollout': (c_int, [c_int, POINTER(c_double), c_int, P, c_int, c_float, c_float, c_uint64,
-                            c_int64, c_uint32, P, P, P, P, c_int, c_int64, P, P, P, P, P, P, P, P,
+                            c_int64, c_uint32, P, P, P, P, P, c_int, c_int64, P, P, P, P, P, P, P, P,
                             P, P]),
     'b2g_policy_sample': (c_int, [P, c_int, c_float, c_uint64, c_int64, c_uint32, P, P, c_int64, P]),
     'b2g_pack_ws_bytes': (c_int64, [c_int]),
@@ -47,7 +49,7 @@ SIGNATURES = {
     'b2g_mlp_minibatch_grad': (c_int, [c_int, c_int, c_int, P, P, c_int64, c_int64, P, P, P, P, P,
                                        c_int, c_int, c_float, c_float, c_float, c_float, P, P, P]),
     'b2g_mlp_eval': (c_int, [c_int, c_int, c_int, P, P, c_int64, c_int64, P, P, P, P, P, P,
-                             c_float, c_int, c_int, c_float, c_float, c_float, c_float, P, P, P]),
+                             P, c_int, c_int, c_float, c_float, c_float, c_float, P, P, P]),
     'b2g_mlp_reduce': (c_int, [P, c_int, c_int, c_float, P, P, P, P, P, P, c_double, c_double,
                                c_double, c_double, P]),
     'b2g_adam_step': (c_int, [P, P, c_float, P, P, P, c_double, c_double, c_double, c_double,

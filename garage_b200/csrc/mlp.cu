@@ -84,7 +84,7 @@ extern "C" int b2g_mlp_minibatch_grad(int obs_dim, int hidden, int out_dim, cons
     else B2G_CHECK_ARG(act && adv && (loss_kind != LOSS_PPO || old_logp), "policy loss needs act, adv (and old_logp for PPO)");
     MlpArgs a{};
     a.params = params; a.idx = idx; a.start = start; a.mb = mb; a.obs = obs; a.act = act;
-    a.adv = adv; a.old_logp = old_logp; a.ret = ret; a.old_mean = nullptr; a.old_log_std = 0.f;
+    a.adv = adv; a.old_logp = old_logp; a.ret = ret; a.old_mean = nullptr; a.old_log_std = nullptr;
     a.loss_kind = loss_kind; a.flags = flags; a.clip = clip; a.ent_coeff = ent_coeff;
     a.min_log_std = min_log_std; a.max_log_std = max_log_std; a.partial = ws_partial;
     a.mean_out = nullptr; a.step_counter = step_counter;
@@ -94,7 +94,7 @@ extern "C" int b2g_mlp_minibatch_grad(int obs_dim, int hidden, int out_dim, cons
 extern "C" int b2g_mlp_eval(int obs_dim, int hidden, int out_dim, const float* params,
                             const int32_t* idx, int64_t start, int64_t n, const float* obs,
                             const float* act, const float* adv, const float* old_logp,
-                            const float* ret, const float* old_mean, float old_log_std,
+                            const float* ret, const float* old_mean, const float* old_log_std,
                             int loss_kind, int flags, float clip, float ent_coeff,
                             float min_log_std, float max_log_std, float* mean_out,
                             float* ws_partial, void* stream) {

@@ -37,7 +37,7 @@ struct MlpArgs {
     const float* old_logp;  // [B]      PPO
     const float* ret;       // [B]      value loss
     const float* old_mean;  // [B,A] or NULL: KL(old || new) statistic
-    float old_log_std;
+    const float* old_log_std;  // device scalar (clamped log-std of the old policy) or NULL
     int loss_kind, flags;
     float clip, ent_coeff, min_log_std, max_log_std;
     float* partial;         // [grid][P + MLP_NSTATS]
@@ -265,7 +265,7 @@ __global__ void __launch_bounds__(MLP_NT, 1) mlp_train_kernel(const MlpArgs a) {
                     for (int q = 0; q < A; ++q) dmu[q] = -dobj_dll * dact[q] / var;
                     if (ls_pass) gLs -= dobj_dll * (dsq / var - (float)A) + dobj_dls;
                     if (a.old_mean) {  // torch kl_normal_normal(old, new), vpg.py:381-406
-                        const float so = expf(a.old_log_std);
+                        const float so = expf(a.old_log_std ? __ldg(a.old_log_std) : 0.0f);
                         const float vr = (so / stdv) * (so / stdv);
 #pragma unroll
                         for (int q = 0; q < A; ++q) {

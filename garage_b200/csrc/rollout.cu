@@ -20,6 +20,7 @@ struct RolloutArgs {
     uint32_t seed_lo, seed_hi;
     int64_t gid0;
     uint32_t t_counter;  // global step counter of row 0 (Philox counter word)
+    const unsigned long long* t_counter_dev;  // optional device-side addend (CUDA-graph replays)
     const float* policy;
     float min_log_std, max_log_std;
     double* state;       // [S,N]
@@ -106,6 +107,7 @@ rollout_kernel(const RolloutArgs a) {
         for (int i = 0; i < O; ++i) ob[i] = 0.0f;
     }
     const uint32_t gid = (uint32_t)(a.gid0 + n);
+    const uint32_t t_base = a.t_counter + (a.t_counter_dev ? (uint32_t)*a.t_counter_dev : 0u);
 
     for (int t = 0; t < a.n_steps; ++t) {
         // ---- layer 1: h1 = tanh(W1 x + b1), x broadcast from the owner lanes
@@ -170,7 +172,7 @@ rollout_kernel(const RolloutArgs a) {
                     for (int q = 0; q < A; ++q) mu[q] = m[g][q];
                 }
             float eps[A], act[A];
-            action_noise<A>(a.seed_lo, a.seed_hi, gid, a.t_counter + (uint32_t)t, eps);
+            action_noise<A>(a.seed_lo, a.seed_hi, gid, t_base + (uint32_t)t, eps);
             float lp = 0.0f;
 #pragma unroll
             for (int q = 0; q < A; ++q) {
@@ -245,7 +247,8 @@ static int launch_rollout(const RolloutArgs& a, cudaStream_t s) {
 extern "C" int b2g_rollout(int env_id, const double* params, int max_episode_length,
                            const float* policy_params, int hidden, float min_log_std,
                            float max_log_std, uint64_t seed, int64_t env_id_offset,
-                           uint32_t t_counter, double* state, float* cur_obs,
+                           uint32_t t_counter, const unsigned long long* t_counter_dev,
+                           double* state, float* cur_obs,
                            int32_t* step_cnt, int32_t* episode, int n_steps, int64_t N,
                            float* obs, float* act, float* rew, float* logp,
                            uint8_t* step_type, float* mean, uint8_t* success,
@@ -260,7 +263,7 @@ extern "C" int b2g_rollout(int env_id, const double* params, int max_episode_len
     if (n_steps == 0 || N == 0) return B2G_OK;
     B2G_CHECK_ARG(policy_params && state && cur_obs && step_cnt && episode && obs && act && rew && logp && step_type, "NULL pointer");
     a.seed_lo = (uint32_t)seed; a.seed_hi = (uint32_t)(seed >> 32);
-    a.gid0 = env_id_offset; a.t_counter = t_counter; a.policy = policy_params;
+    a.gid0 = env_id_offset; a.t_counter = t_counter; a.t_counter_dev = t_counter_dev; a.policy = policy_params;
     a.min_log_std = min_log_std; a.max_log_std = max_log_std;
     a.state = state; a.cur_obs = cur_obs; a.step_cnt = step_cnt; a.episode = episode;
     a.n_steps = n_steps; a.N = N;

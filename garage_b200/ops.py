@@ -198,8 +198,13 @@ class RolloutBuffers:
         self.ep_len = torch.empty(T, n, dtype=torch.int32, device=device)
 
 
+def counter_add(counter, delta):
+    with torch.cuda.device(counter.device):
+        call('b2g_counter_add', ptr(counter), int(delta), _stream(counter))
+
+
 def rollout(es, params, max_episode_length, policy_flat, hidden, min_log_std, max_log_std, seed,
-            env_id_offset, t_counter, buf, t0, n_steps):
+            env_id_offset, t_counter, buf, t0, n_steps, t_counter_dev=None):
     """b2g_rollout for rows t0..t0+n_steps of `buf`."""
     _chk(policy_flat, torch.float32, 'policy_flat')
     if t0 + n_steps > buf.T:
@@ -211,7 +216,7 @@ def rollout(es, params, max_episode_length, policy_flat, hidden, min_log_std, ma
     with torch.cuda.device(es.device):
         call('b2g_rollout', es.env_id, params, int(max_episode_length or 0), ptr(policy_flat),
              int(hidden), float(min_log_std), float(max_log_std), int(seed) & (2**64 - 1),
-             int(env_id_offset), int(t_counter) & 0xffffffff, ptr(es.state), ptr(es.obs),
+             int(env_id_offset), int(t_counter) & 0xffffffff, ptr(t_counter_dev), ptr(es.state), ptr(es.obs),
              ptr(es.step_cnt), ptr(es.episode), int(n_steps), es.n, ptr(row(buf.obs)),
              ptr(row(buf.act)), ptr(row(buf.rew)), ptr(row(buf.logp)), ptr(row(buf.step_type)),
              ptr(row(buf.mean)), ptr(row(buf.success)), ptr(row(buf.last_obs)),
@@ -231,8 +236,9 @@ def policy_sample(mean, log_std, seed, env_id_offset, t_counter, want_logp=True)
 
 
 # ------------------------------------------------------------------ pack --
-def pack_plan(step_type, ep_len, T, num_samples):
-    """Returns (ws, (t_star, n_eps, n_steps, reached)) -- one small D2H sync."""
+def pack_plan(step_type, ep_len, T, num_samples, sync=True):
+    """Row statistics + cut row.  sync=True returns (ws, (t_star, n_eps, n_steps, reached)) after
+    one small D2H copy; sync=False returns (ws, summary_device_tensor) without synchronising."""
     _chk(step_type, torch.uint8, 'step_type')
     _chk(ep_len, torch.int32, 'ep_len')
     N = step_type.shape[1]
@@ -242,6 +248,8 @@ def pack_plan(step_type, ep_len, T, num_samples):
     with torch.cuda.device(dev):
         call('b2g_pack_plan', ptr(step_type), ptr(ep_len), int(T), int(N), int(num_samples), ptr(ws),
              ptr(summary), _stream(step_type))
+    if not sync:
+        return ws, summary
     t_star, n_eps, n_steps, reached = (int(v) for v in summary.tolist())
     return ws, (t_star, n_eps, n_steps, bool(reached))
 
@@ -329,18 +337,19 @@ def mlp_minibatch_grad(shape, params, obs, *, idx=None, start=0, mb=None, act=No
 
 
 def mlp_eval(shape, params, obs, *, idx=None, start=0, n=None, act=None, adv=None, old_logp=None,
-             ret=None, old_mean=None, old_log_std=0.0, loss_kind=LOSS_NONE, flags=0, clip=0.2,
+             ret=None, old_mean=None, old_log_std=None, loss_kind=LOSS_NONE, flags=0, clip=0.2,
              ent_coeff=0.0, min_log_std=-INF, max_log_std=INF, mean_out=None):
     _chk(params, torch.float32, 'params')
     _chk(obs, torch.float32, 'obs')
     _chk(idx, torch.int32, 'idx')
     _chk(mean_out, torch.float32, 'mean_out')
+    _chk(old_log_std, torch.float32, 'old_log_std')
     if n is None:
         n = idx.numel() if idx is not None else obs.shape[0] - start
     with torch.cuda.device(shape.device):
         call('b2g_mlp_eval', shape.O, shape.H, shape.A, ptr(params), ptr(idx), int(start), int(n),
              ptr(obs), ptr(act), ptr(adv), ptr(old_logp), ptr(ret), ptr(old_mean),
-             float(old_log_std), int(loss_kind), int(flags), float(clip), float(ent_coeff),
+             ptr(old_log_std), int(loss_kind), int(flags), float(clip), float(ent_coeff),
              float(min_log_std), float(max_log_std), ptr(mean_out), ptr(shape.ws), _stream(params))
     return shape.num_partials(False, n)
 
@@ -361,3 +370,14 @@ def adam_step(params, grad, grad_scale, adam_m, adam_v, step_counter, lr, beta1=
         call('b2g_adam_step', ptr(params), ptr(grad), float(grad_scale), ptr(adam_m), ptr(adam_v),
              ptr(step_counter), float(lr), float(beta1), float(beta2), float(eps),
              int(params.numel()), _stream(params))
+
+
+def permutation(n, seed, counter=0, counter_dev=None, out=None, device=None):
+    """Random permutation of 0..n-1 (int32) from (seed, counter [+ *counter_dev])."""
+    if out is None:
+        out = torch.empty(n, dtype=torch.int32, device=device)
+    _chk(out, torch.int32, 'out')
+    with torch.cuda.device(out.device):
+        call('b2g_permutation', int(seed) & (2**64 - 1), ptr(counter_dev), int(counter), int(n),
+             ptr(out), _stream(out))
+    return out

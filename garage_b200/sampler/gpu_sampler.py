@@ -1,0 +1,250 @@
+"""GPU sampler: `Sampler.obtain_samples` (reference sampler/sampler.py:73-93) with
+the semantics of `LocalSampler` + `VecWorker` (sampler/local_sampler.py:134-166,
+sampler/vec_worker.py:107-219), executed by ONE persistent rollout kernel per
+chunk of time steps and assembled into an EpisodeBatch by the pack kernels.
+
+Semantics kept from the reference:
+  * every `obtain_samples` pushes the agent update and therefore restarts all
+    environments from `reset()` (vec_worker.py:72-73,107-137); partial episodes
+    of the previous call are discarded;
+  * the batch holds whole episodes only, in completion order (ties in env
+    order), and ends with the first time step at which the number of completed
+    samples reaches `num_samples` (all episodes finishing in that step included);
+  * `total_env_steps` accumulates `sum(lengths)`.
+"""
+import abc
+import math
+
+import numpy as np
+import psutil
+import torch
+
+from garage_b200 import ops
+from garage_b200._dtypes import DeviceEpisodeBatch
+from garage_b200.experiment import deterministic
+
+
+class _LazyLogStd:
+    """Clamped log-std of the rollout policy, snapshotted on the device (async) and
+    read back only if somebody asks for agent_infos['log_std']."""
+
+    def __init__(self, module):
+        self._snap = module.flat[0:1].clone()
+        self._lo, self._hi = module.min_log_std, module.max_log_std
+        self.device_value = self._snap.clamp(min=self._lo, max=self._hi)
+
+    def __float__(self):
+        return min(max(float(self._snap.item()), self._lo), self._hi)
+
+
+class Sampler(abc.ABC):
+    """Reference sampler/sampler.py:7-100."""
+
+    @abc.abstractmethod
+    def obtain_samples(self, itr, num_samples, agent_update, env_update=None):
+        pass
+
+    @abc.abstractmethod
+    def shutdown_worker(self):
+        pass
+
+
+class VecWorker:
+    """Marker accepted as `worker_class=` for source compatibility: the GPU sampler
+    IS a vectorised worker; `worker_args={'n_envs': k}` sets envs per worker."""
+    DEFAULT_N_ENVS = 8
+
+
+class GPUSampler(Sampler):
+    """Drop-in for `LocalSampler(agents, envs, max_episode_length=, n_workers=,
+    worker_class=VecWorker, worker_args={'n_envs': k})`; the total number of
+    environment copies is `n_envs` if given, else `n_workers * worker_args['n_envs']`.
+
+    Args:
+        agents (GaussianMLPPolicy): the policy (its flat CUDA parameter vector is used).
+        envs (BatchedEnv): environment description (PointEnv / PendulumEnv / CartPoleEnv).
+        max_episode_length (int): required, like the reference (local_sampler.py:63-65).
+        n_envs (int): environment copies on this rank.
+        seed (int): Philox key (defaults to `deterministic.get_seed()` or 0).
+        env_id_offset (int): global id of this rank's first env (rank * n_envs), so
+            results do not depend on how envs are sharded over GPUs.
+    """
+
+    def __init__(self, agents, envs, *, worker_factory=None, max_episode_length=None,
+                 is_tf_worker=False, seed=None, n_workers=None, worker_class=VecWorker,
+                 worker_args=None, n_envs=None, env_id_offset=0, keep_agent_infos=True):
+        if worker_factory is None and max_episode_length is None:
+            raise TypeError('Must construct a sampler from WorkerFactory or parameters (at least '
+                            'max_episode_length)')
+        if is_tf_worker:
+            raise NotImplementedError('TF workers are out of scope of garage_b200')
+        if isinstance(agents, (list, tuple)) or isinstance(envs, (list, tuple)):
+            raise NotImplementedError('GPUSampler takes one policy and one env description; the env '
+                                      'copies are made on the device')
+        if n_envs is None:
+            per = (worker_args or {}).get('n_envs', VecWorker.DEFAULT_N_ENVS)
+            n_envs = per * (n_workers if n_workers is not None else psutil.cpu_count(logical=False))
+        if n_envs <= 0:
+            raise ValueError('n_envs must be positive')
+        self._policy = agents
+        self._env = envs
+        self._max_episode_length = max_episode_length
+        self._n_envs = int(n_envs)
+        if seed is None:
+            seed = deterministic.get_seed()
+        self._seed = 0 if seed is None else int(seed)
+        self._env_id_offset = int(env_id_offset)
+        self._keep_agent_infos = keep_agent_infos
+        self._t_dev = None  # device-side global step counter (Philox counter word)
+        self._es = None
+        self._buf = None
+        self.total_env_steps = 0
+
+    @classmethod
+    def from_worker_factory(cls, worker_factory, agents, envs):
+        return cls(agents, envs, max_episode_length=worker_factory.max_episode_length,
+                   seed=getattr(worker_factory, 'seed', None), n_workers=worker_factory.n_workers,
+                   worker_args=getattr(worker_factory, 'worker_args', None))
+
+    # ------------------------------------------------------------------ helpers --
+    @property
+    def n_envs(self):
+        return self._n_envs
+
+    def _device(self):
+        return self._policy.flat.device
+
+    def _max_len(self):
+        m = self._max_episode_length
+        if m is None or (isinstance(m, float) and math.isinf(m)):
+            return 0
+        return int(m)
+
+    def _ensure_state(self):
+        if self._es is None or self._es.env_id != self._env.env_id:
+            self._es = ops.EnvState(self._env.env_id, self._n_envs, self._device())
+        if self._t_dev is None:
+            self._t_dev = torch.zeros(1, dtype=torch.int64, device=self._device())
+
+    def _ensure_buffers(self, rows):
+        if self._buf is None or self._buf.T < rows or self._buf.obs.device != self._device():
+            old = self._buf
+            self._buf = ops.RolloutBuffers(self._env.env_id, rows, self._n_envs, self._device(),
+                                           want_mean=self._keep_agent_infos,
+                                           want_success=self._env.has_success)
+            return old
+        return None
+
+    def _update(self, agent_update, env_update):
+        if agent_update is not None:
+            if isinstance(agent_update, dict):
+                self._policy.set_param_values(agent_update)
+            elif agent_update is not self._policy:
+                self._policy.set_param_values(agent_update.get_param_values())
+        if env_update is not None:
+            if not hasattr(env_update, 'env_id'):
+                raise TypeError('env_update must be a garage_b200 BatchedEnv; got {}'.format(type(env_update)))
+            self._env = env_update
+            self._es = None
+            self._buf = None
+
+    # -------------------------------------------------------------------- API --
+    def obtain_samples(self, itr, num_samples, agent_update, env_update=None):
+        """Collect at least `num_samples` transitions (reference
+        local_sampler.py:134-166).  Returns a DeviceEpisodeBatch."""
+        self._update(agent_update, env_update)
+        env, N = self._env, self._n_envs
+        L = self._max_len()
+        if L == 0 and getattr(env, 'never_terminates', False):
+            raise ValueError('an env that never terminates needs a finite max_episode_length')
+        self._ensure_state()
+        prm = env.params_array()
+        pol = self._policy
+        # update_agent -> every env restarts from reset() (vec_worker.py:107-137)
+        ops.env_reset(self._es, prm, self._seed, self._env_id_offset)
+        static = bool(getattr(env, 'never_terminates', False)) and L > 0
+        if static:
+            rows = int(math.ceil(num_samples / float(N * L))) * L
+        else:
+            rows = int(math.ceil(num_samples / float(N)))
+            if L:
+                rows = int(math.ceil(rows / float(L))) * L
+        rows = max(rows, 1)
+        self._ensure_buffers(rows)
+        done_rows = 0
+        while True:
+            ops.rollout(self._es, prm, L, pol.flat, pol.mlp_shape.H, pol._module.min_log_std,
+                        pol._module.max_log_std, self._seed, self._env_id_offset, 0,
+                        self._buf, done_rows, rows - done_rows, t_counter_dev=self._t_dev)
+            ops.counter_add(self._t_dev, rows - done_rows)
+            done_rows = rows
+            if static:
+                t_star, n_eps, n_steps = rows - 1, N * (rows // L), N * rows
+                ws, _ = self._plan(rows, num_samples, sync=False)
+                break
+            ws, (t_star, n_eps, n_steps, reached) = self._plan(rows, num_samples, sync=True)
+            if reached:
+                break
+            # not enough completed samples yet: keep the envs running (local_sampler.py:158-166)
+            more = max(L if L else 64, rows // 2)
+            old = self._buf
+            self._buf = None
+            self._ensure_buffers(rows + more)
+            for name in ('obs', 'act', 'rew', 'logp', 'step_type', 'mean', 'success', 'last_obs', 'ep_len'):
+                src = getattr(old, name)
+                if src is not None:
+                    getattr(self._buf, name)[:rows].copy_(src[:rows])
+            rows += more
+        batch = self._pack(ws, rows, t_star, n_eps, n_steps, static)
+        self.total_env_steps += n_steps
+        return batch
+
+    def _plan(self, rows, num_samples, sync):
+        b = self._buf
+        return ops.pack_plan(b.step_type[:rows], b.ep_len[:rows], rows, num_samples, sync=sync)
+
+    def _pack(self, ws, rows, t_star, n_eps, n_steps, static):
+        b, env, pol = self._buf, self._env, self._policy
+        lengths, ep_off, last_obs, ep_env, ep_end = ops.pack_index(
+            b.step_type, b.ep_len, b.last_obs, ws, rows, t_star, n_eps)
+        fields = [b.obs, b.act, b.rew, b.logp, b.step_type]
+        if b.mean is not None:
+            fields.append(b.mean)
+        if b.success is not None:
+            fields.append(b.success)
+        packed = ops.pack_fields(b.step_type, b.ep_len, ep_off, t_star, n_steps, fields)
+        dev = DeviceEpisodeBatch._Dev()
+        dev.observations, dev.actions, dev.rewards, dev.logp, dev.step_types = packed[:5]
+        k = 5
+        dev.mean = None
+        if b.mean is not None:
+            dev.mean = packed[k]
+            k += 1
+        dev.success = packed[k] if b.success is not None else None
+        dev.last_observations, dev.lengths = last_obs, lengths
+        dev.ep_env, dev.ep_end = ep_env, ep_end
+        return DeviceEpisodeBatch(
+            env_spec=env.spec, dev=dev, n_eps=n_eps, n_steps=n_steps,
+            log_std=_LazyLogStd(pol._module), tm=b, ep_off=ep_off, t_star=t_star,
+            episode_info_consts=env.episode_info(), env_info_consts=env.env_info_consts(),
+            lengths_host=np.full(n_eps, self._max_len(), dtype=np.int64) if static else None)
+
+    def obtain_exact_episodes(self, n_eps_per_worker, agent_update, env_update=None):
+        """`n_eps_per_worker` whole episodes from EVERY env copy, env-major order
+        (reference local_sampler.py:168-200 with one env per worker)."""
+        raise NotImplementedError('obtain_exact_episodes is not on the PPO/VPG path; use obtain_samples')
+
+    def shutdown_worker(self):
+        """Nothing to shut down: there are no worker processes."""
+        self._es = None
+        self._buf = None
+
+    def __getstate__(self):  # cloudpickle-able: device buffers are rebuilt lazily
+        state = self.__dict__.copy()
+        state['_es'] = None
+        state['_buf'] = None
+        state['_t_dev'] = None
+        return state
+
+
+LocalSampler = GPUSampler

@@ -1,0 +1,4 @@
+from garage_b200.torch.algos.ppo import PPO
+from garage_b200.torch.algos.vpg import VPG
+
+__all__ = ['VPG', 'PPO']

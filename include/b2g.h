@@ -41,6 +41,8 @@ extern "C" {
 #define B2G_STEP_TIMEOUT 3
 
 int b2g_version(void);
+/* *counter += delta on the stream (device-side step/epoch counters of graph replays) */
+int b2g_counter_add(unsigned long long* counter, unsigned long long delta, void* stream);
 const char* b2g_last_error(void);
 /* number of SMs of the current device (grid sizing is a multiple of it) */
 int b2g_device_sm_count(void);
@@ -160,8 +162,10 @@ int64_t b2g_mlp_param_count(int obs_dim, int hidden, int out_dim);
  *     episode[N] (as b2g_env_reset leaves them).
  *   min/max_log_std: log(min_std) / log(max_std) clamps of
  *     gaussian_mlp_module.py:171-176 (+-INFINITY for None).
- *   Philox counter = (env_id_offset + n, t_counter + t): results do not depend
- *     on how envs are sharded over ranks or on chunking over time.
+ *   Philox counter = (env_id_offset + n, t_counter + *t_counter_dev + t): results
+ *     do not depend on how envs are sharded over ranks or on chunking over time.
+ *     t_counter_dev (device u64, may be NULL) lets a captured CUDA graph advance
+ *     the stream between replays (b2g_counter_add).
  *   out, time-major rows t = 0..n_steps-1: obs[T,N,O] (observation the action
  *     was computed from), act[T,N,A] (un-clipped sample), rew[T,N] f32,
  *     logp[T,N] (log-prob of act under the rollout policy == PPO's old_ll, Q8),
@@ -175,7 +179,8 @@ int64_t b2g_mlp_param_count(int obs_dim, int hidden, int out_dim);
  */
 int b2g_rollout(int env_id, const double* params, int max_episode_length,
                 const float* policy_params, int hidden, float min_log_std, float max_log_std,
-                uint64_t seed, int64_t env_id_offset, uint32_t t_counter, double* state,
+                uint64_t seed, int64_t env_id_offset, uint32_t t_counter,
+                const unsigned long long* t_counter_dev, double* state,
                 float* cur_obs, int32_t* step_cnt, int32_t* episode, int n_steps, int64_t N,
                 float* obs, float* act, float* rew, float* logp, uint8_t* step_type,
                 float* mean, uint8_t* success, float* last_obs, int32_t* ep_len, void* stream);
@@ -261,13 +266,14 @@ int b2g_mlp_minibatch_grad(int obs_dim, int hidden, int out_dim, const float* pa
 
 /* Forward only over n rows: mean_out[n,out_dim] (may be NULL; policy means /
  * value baselines, vpg.py:155-156) and the same statistics as above, plus
- * sum KL(old || new) when old_mean[B,out_dim] is given (vpg.py:381-406, the old
- * policy is the rollout policy, Q8).  n_partials =
+ * sum KL(old || new) when old_mean[B,out_dim] and old_log_std (DEVICE scalar, the
+ * old policy's clamped log-std) are given (vpg.py:381-406; the old policy is
+ * the rollout policy, Q8).  n_partials =
  * b2g_mlp_num_partials(..., 0, n). */
 int b2g_mlp_eval(int obs_dim, int hidden, int out_dim, const float* params, const int32_t* idx,
                  int64_t start, int64_t n, const float* obs, const float* act, const float* adv,
                  const float* old_logp, const float* ret, const float* old_mean,
-                 float old_log_std, int loss_kind, int flags, float clip, float ent_coeff,
+                 const float* old_log_std, int loss_kind, int flags, float clip, float ent_coeff,
                  float min_log_std, float max_log_std, float* mean_out, float* ws_partial,
                  void* stream);
 
@@ -285,6 +291,15 @@ int b2g_mlp_reduce(const float* ws_partial, int n_partials, int n_params, float 
 int b2g_adam_step(float* params, const float* grad, float grad_scale, float* adam_m,
                   float* adam_v, const unsigned long long* step_counter, double lr, double beta1,
                   double beta2, double eps, int n, void* stream);
+
+/* Random permutation of 0..n-1 as int32 ids (minibatch shuffle; stands in for
+ * np.random.shuffle(self._ids), np/optimizers/minibatch_dataset.py:35, in
+ * throughput mode -- parity mode passes the reference's own id lists to
+ * b2g_mlp_minibatch_grad instead).  Keyed Feistel network + cycle walking, key =
+ * Philox(seed; counter + *counter_dev): no sort, no state, graph-capturable
+ * (counter_dev may be NULL). */
+int b2g_permutation(uint64_t seed, const unsigned long long* counter_dev, uint64_t counter,
+                    int64_t n, int32_t* out, void* stream);
 
 #ifdef __cplusplus
 }

@@ -1,0 +1,170 @@
+"""End-to-end on the GPU through the garage-compatible API: sampler -> EpisodeBatch ->
+PPO/VPG._train_once -> Trainer."""
+import math
+
+import numpy as np
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+REF_POLICY_KEYS = [
+    '_module._init_std',
+    '_module._mean_module._layers.0.linear.weight', '_module._mean_module._layers.0.linear.bias',
+    '_module._mean_module._layers.1.linear.weight', '_module._mean_module._layers.1.linear.bias',
+    '_module._mean_module._output_layers.0.linear.weight',
+    '_module._mean_module._output_layers.0.linear.bias',
+    '_module.min_std_param',
+]
+
+
+def build(env, hidden=(64, 64), n_envs=64, algo='ppo', epochs=2, mb=None, **algo_kw):
+    from garage_b200.sampler import GPUSampler
+    from garage_b200.torch.algos import PPO, VPG
+    from garage_b200.torch.optimizers import OptimizerWrapper
+    from garage_b200.torch.policies import GaussianMLPPolicy
+    from garage_b200.torch.value_functions import GaussianMLPValueFunction
+    torch.manual_seed(1)
+    policy = GaussianMLPPolicy(env.spec, hidden_sizes=hidden)
+    vf = GaussianMLPValueFunction(env.spec, hidden_sizes=hidden)
+    sampler = GPUSampler(policy, env, max_episode_length=env.spec.max_episode_length, n_envs=n_envs,
+                         seed=1234)
+    po = OptimizerWrapper((torch.optim.Adam, dict(lr=2.5e-4)), policy, max_optimization_epochs=epochs,
+                          minibatch_size=mb)
+    vo = OptimizerWrapper((torch.optim.Adam, dict(lr=2.5e-4)), vf, max_optimization_epochs=epochs,
+                          minibatch_size=mb)
+    cls = PPO if algo == 'ppo' else VPG
+    a = cls(env.spec, policy, vf, sampler, policy_optimizer=po, vf_optimizer=vo, discount=0.99,
+            gae_lambda=0.95, **algo_kw)
+    return a, policy, vf, sampler
+
+
+def test_state_dict_keys_match_reference():
+    from garage_b200.envs import PointEnv
+    from garage_b200.torch.policies import GaussianMLPPolicy
+    from garage_b200.torch.value_functions import GaussianMLPValueFunction
+    env = PointEnv(max_episode_length=50)
+    pol = GaussianMLPPolicy(env.spec)
+    sd = pol.state_dict()
+    assert list(sd.keys()) == REF_POLICY_KEYS
+    assert sd['_module._mean_module._layers.0.linear.weight'].shape == (32, 3)
+    assert sd['_module._mean_module._output_layers.0.linear.weight'].shape == (2, 32)
+    assert sd['_module._init_std'].shape == (1, )
+    vf = GaussianMLPValueFunction(env.spec)
+    assert list(vf.state_dict().keys()) == [k.replace('_module.', 'module.', 1) for k in REF_POLICY_KEYS[:-1]]
+    # parameters are views of the flat vector the kernels use: a CPU state_dict loads through
+    cpu = {k: torch.randn_like(v).cpu() for k, v in sd.items() if 'min_std' not in k}
+    cpu['_module.min_std_param'] = sd['_module.min_std_param'].cpu()
+    pol.set_param_values(cpu)
+    assert torch.equal(pol.flat[0:1].cpu(), cpu['_module._init_std'])
+    assert torch.equal(pol.flat[1:1 + 96].cpu(), cpu['_module._mean_module._layers.0.linear.weight'].reshape(-1))
+    # xavier/zeros initialisation as in the reference: zero biases, log_std = log(1) = 0
+    pol2 = GaussianMLPPolicy(env.spec)
+    assert float(pol2.flat[0]) == 0.0
+    assert torch.count_nonzero(pol2.state_dict()['_module._mean_module._layers.0.linear.bias']) == 0
+
+
+def test_get_actions_api():
+    from garage_b200.envs import PointEnv
+    from garage_b200.torch.policies import GaussianMLPPolicy
+    env = PointEnv(max_episode_length=50)
+    pol = GaussianMLPPolicy(env.spec)
+    obs, _ = env.reset()
+    a, info = pol.get_action(obs)
+    assert a.shape == (2, ) and info['mean'].shape == (2, ) and info['log_std'].shape == (2, )
+    acts, infos = pol.get_actions(np.stack([obs] * 5))
+    assert acts.shape == (5, 2) and infos['mean'].shape == (5, 2)
+    assert np.allclose(infos['mean'][0], infos['mean'][4]) and np.allclose(infos['log_std'], 0.0)
+    dist, info = pol(torch.from_numpy(np.stack([obs] * 3)))
+    assert dist.mean.shape == (3, 2) and np.allclose(dist.mean.cpu().numpy(), infos['mean'][:3], atol=1e-6)
+    es = env.step(a)
+    assert es.observation.shape == (3, ) and isinstance(es.reward, float)
+
+
+def test_sampler_semantics_vecworker():
+    """161 samples, max length 16, 8 env copies: the VecWorker loop completes 8 episodes
+    per 16 steps -> 16 whole episodes (256 steps), in env order inside each completion row."""
+    from garage_b200 import EpisodeBatch
+    from garage_b200.envs import PointEnv
+    from garage_b200.sampler import LocalSampler
+    from garage_b200.torch.policies import GaussianMLPPolicy
+    env = PointEnv(max_episode_length=16)
+    pol = GaussianMLPPolicy(env.spec)
+    s = LocalSampler(agents=pol, envs=env, max_episode_length=16, n_envs=8)
+    eps = s.obtain_samples(0, 161, pol.get_param_values())
+    assert list(eps.lengths) == [16] * 16 and eps.lengths.dtype == np.int64
+    assert s.total_env_steps == 256
+    assert eps.observations.shape == (256, 3) and eps.observations.dtype == np.float32
+    assert eps.rewards.dtype == np.float64 and eps.actions.shape == (256, 2)
+    st = eps.step_types
+    assert st[0] == 0 and st[15] == 3 and (st[1:15] == 1).all()
+    assert set(eps.agent_infos) == {'mean', 'log_std'} and 'success' in eps.env_infos
+    assert eps.episode_infos_by_episode['goal'].shape == (16, 2)
+    assert eps.padded_observations.shape == (16, 16, 3) and eps.valids.shape == (16, 16)
+    host = eps.to_host()
+    assert isinstance(host, EpisodeBatch) and len(host.split()) == 16
+    # first observation of every episode is the reset observation (0, 0, |goal|)
+    first = eps.observations[::16]
+    assert np.allclose(first, [[0, 0, math.sqrt(2)]] * 16)
+    # next_observations ends with last_observations
+    assert np.array_equal(eps.next_observations[15], eps.last_observations[0])
+    with pytest.raises(TypeError):
+        LocalSampler(agents=pol, envs=env)
+
+
+@pytest.mark.parametrize('algo,mb', [('ppo', 2000), ('ppo', None), ('vpg', None)])
+def test_train_once_pendulum(algo, mb):
+    from garage_b200.envs import PendulumEnv
+    env = PendulumEnv(max_episode_length=50)
+    a, policy, vf, sampler = build(env, n_envs=128, algo=algo, mb=mb)
+    before = policy.flat.clone()
+    eps = sampler.obtain_samples(0, 128 * 50, policy.get_param_values())
+    assert eps.n_steps == 6400 and eps.n_episodes == 128
+    r = a._train_once(0, eps)
+    s = a.last_stats
+    assert np.isfinite(r) and r < 0
+    assert abs(s['GaussianMLPPolicy/KLBefore']) < 1e-6
+    assert s['GaussianMLPPolicy/KL'] >= 0 and s['GaussianMLPPolicy/KL'] < 0.1
+    assert abs(s['GaussianMLPPolicy/Entropy'] - (0.5 + 0.5 * math.log(2 * math.pi))) < 1e-2
+    assert s['GaussianMLPValueFunction/LossAfter'] < s['GaussianMLPValueFunction/LossBefore']
+    assert s['Evaluation/NumEpisodes'] == 128 and s['Evaluation/TerminationRate'] == 0.0
+    assert not torch.equal(before, policy.flat)
+    # log_performance cross-check on the host copy of the batch
+    und = eps.rewards.reshape(128, 50).sum(1)
+    assert abs(s['Evaluation/AverageReturn'] - und.mean()) < 1e-3 * abs(und.mean())
+    assert abs(s['Evaluation/MaxReturn'] - und.max()) < 1e-3 * abs(und.max())
+
+
+def test_trainer_loop_cartpole_vpg_and_point_ppo():
+    from garage_b200 import Trainer
+    from garage_b200.envs import CartPoleEnv, PointEnv
+    env = CartPoleEnv(max_episode_length=100)
+    a, policy, vf, sampler = build(env, n_envs=256, algo='vpg', epochs=1)
+    tr = Trainer()
+    tr.setup(a, env)
+    ret = tr.train(n_epochs=3, batch_size=5000)
+    assert np.isfinite(ret) and 5 < ret <= 100
+    assert tr.total_env_steps >= 15000 and len(tr.log) == 3
+    assert 0 < tr.log[-1]['Evaluation/TerminationRate'] <= 1.0
+    env = PointEnv(max_episode_length=30)
+    a, policy, vf, sampler = build(env, hidden=(32, 32), n_envs=64, algo='ppo', epochs=2, mb=512)
+    tr = Trainer()
+    tr.setup(a, env)
+    ret = tr.train(n_epochs=2, batch_size=1000)
+    assert np.isfinite(ret) and 'Evaluation/SuccessRate' in tr.log[-1]
+
+
+def test_ppo_learns_point_env():
+    """Reference-style 'does it learn' check (tests/garage/torch/algos/test_ppo.py is a
+    MuJoCo learning test): mean return on PointEnv improves markedly."""
+    from garage_b200 import Trainer
+    from garage_b200.envs import PointEnv
+    env = PointEnv(max_episode_length=40)
+    a, policy, vf, sampler = build(env, hidden=(32, 32), n_envs=512, algo='ppo', epochs=4, mb=4096)
+    a._policy_optimizer.lr = 3e-3
+    a._vf_optimizer.lr = 3e-3
+    tr = Trainer()
+    tr.setup(a, env)
+    tr.train(n_epochs=40, batch_size=512 * 40)
+    first, last = tr.log[0]['Evaluation/AverageReturn'], tr.log[-1]['Evaluation/AverageReturn']
+    assert last > first + 10, (first, last)

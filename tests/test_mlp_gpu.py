@@ -125,7 +125,7 @@ def test_forward_means_kl_entropy():
     t = lambda a: torch.from_numpy(a).to(dev)
     mean_out = torch.empty(n, A, device=dev)
     nb = ops.mlp_eval(sh, t(flat), t(obs), act=t(act), adv=t(adv), old_logp=t(old_logp),
-                      old_mean=t(old_mean), old_log_std=old_ls, loss_kind=ops.LOSS_PPO,
+                      old_mean=t(old_mean), old_log_std=torch.tensor([old_ls], dtype=torch.float32, device=dev), loss_kind=ops.LOSS_PPO,
                       min_log_std=math.log(1e-6), mean_out=mean_out)
     stats = torch.empty(8, dtype=torch.float64, device=dev)
     ops.mlp_reduce(sh, nb, 1.0, stats_out=stats)
