@@ -314,33 +314,33 @@ class DeviceEpisodeBatch(EpisodeBatch):
 
     @property
     def lengths(self):
-        return self._get('lengths', lambda: self.dev.lengths.cpu().numpy())
+        return self._get('lengths', lambda: self._host('lengths'))
 
     @property
     def observations(self):
-        return self._get('observations', lambda: self.dev.observations.cpu().numpy())
+        return self._get('observations', lambda: self._host('observations'))
 
     @property
     def last_observations(self):
-        return self._get('last_observations', lambda: self.dev.last_observations.cpu().numpy())
+        return self._get('last_observations', lambda: self._host('last_observations'))
 
     @property
     def actions(self):
-        return self._get('actions', lambda: self.dev.actions.cpu().numpy())
+        return self._get('actions', lambda: self._host('actions'))
 
     @property
     def rewards(self):
         # python floats in the reference -> float64 (Q9)
-        return self._get('rewards', lambda: self.dev.rewards.cpu().numpy().astype(np.float64))
+        return self._get('rewards', lambda: self._host('rewards').astype(np.float64))
 
     @property
     def step_types(self):
-        return self._get('step_types', lambda: step_types_from_codes(self.dev.step_types.cpu().numpy()))
+        return self._get('step_types', lambda: step_types_from_codes(self._host('step_types')))
 
     @property
     def agent_infos(self):
         def make():
-            mean = self.dev.mean.cpu().numpy()
+            mean = self._host('mean')
             return dict(mean=mean, log_std=np.full_like(mean, np.float32(self.log_std)))
         return self._get('agent_infos', make)
 
@@ -362,6 +362,46 @@ class DeviceEpisodeBatch(EpisodeBatch):
         return self._get('episode_infos_by_episode', lambda: {
             k: np.broadcast_to(np.asarray(v), (self.n_episodes, ) + np.shape(v)).copy()
             for k, v in self._episode_info_consts.items()})
+
+    _pinned_pool = {}
+
+    def prefetch_host(self, fields=('observations', 'actions', 'rewards', 'step_types', 'mean',
+                                    'last_observations', 'lengths')):
+        """Start asynchronous D2H copies of the packed fields into pinned host buffers on a
+        side stream (they overlap with whatever is enqueued next, e.g. `_train_once`).
+        The NumPy attributes then wait for the copy instead of doing a pageable `.cpu()`.
+        The pinned buffers are pooled: the arrays are valid until the next `prefetch_host`
+        of a batch of the same shape.  Returns the number of bytes copied."""
+        cur = torch.cuda.current_stream(self.dev.observations.device)
+        side = DeviceEpisodeBatch._pinned_pool.setdefault(('stream', cur.device), torch.cuda.Stream(cur.device))
+        side.wait_stream(cur)
+        self._pinned = {}
+        nbytes = 0
+        with torch.cuda.stream(side):
+            for name in fields:
+                t = getattr(self.dev, name, None)
+                if t is None:
+                    continue
+                key = (name, tuple(t.shape), t.dtype)
+                buf = DeviceEpisodeBatch._pinned_pool.get(key)
+                if buf is None:
+                    buf = torch.empty(t.shape, dtype=t.dtype, pin_memory=True)
+                    DeviceEpisodeBatch._pinned_pool[key] = buf
+                buf.copy_(t, non_blocking=True)
+                t.record_stream(side)
+                self._pinned[name] = buf
+                nbytes += t.numel() * t.element_size()
+            self._pinned_event = torch.cuda.Event()
+            self._pinned_event.record(side)
+        return nbytes
+
+    def _host(self, name):
+        """NumPy view of a prefetched field, or a synchronous copy."""
+        pinned = getattr(self, '_pinned', None)
+        if pinned and name in pinned:
+            self._pinned_event.synchronize()
+            return pinned[name].numpy()
+        return getattr(self.dev, name).cpu().numpy()
 
     def to_host(self):
         """A plain, validated `EpisodeBatch` copy (all fields on the host)."""

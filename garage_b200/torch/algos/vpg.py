@@ -358,23 +358,32 @@ class VPG(RLAlgorithm):
             out[6] = float('nan')
         return und
 
-    def _train_once(self, itr, eps):
-        """One policy-optimisation iteration (reference vpg.py:136-206).
-
-        Returns:
-            numpy.float64: mean undiscounted return of the batch.
-        """
+    def _enqueue_iteration(self, eps):
+        """Everything of `_train_once` that runs on the device, without any host
+        synchronisation (CUDA-graph capturable when the batch shape is static).
+        Returns (stats [40] float64 device tensor, B, n_eps)."""
         f = self._prepare(eps)
-        device = f.obs.device
-        stats = torch.zeros(40, dtype=torch.float64, device=device)
+        stats = torch.zeros(40, dtype=torch.float64, device=f.obs.device)
         if self._log_stats:
             self._evaluate(f, stats[0:16])
         self._train(f)
         if self._log_stats:
             self._evaluate(f, stats[16:32])
         self._performance(f, stats[32:39])
-        s = stats.cpu().numpy()  # the single D2H read of the iteration
-        B = float(f.B)
+        return stats, f.B, f.n_eps
+
+    def _train_once(self, itr, eps):
+        """One policy-optimisation iteration (reference vpg.py:136-206).
+
+        Returns:
+            numpy.float64: mean undiscounted return of the batch.
+        """
+        stats, B, n_eps = self._enqueue_iteration(eps)
+        return self._log_iteration(itr, stats.cpu().numpy(), B, n_eps)  # the single D2H read
+
+    def _log_iteration(self, itr, s, B, n_eps):
+        """The dowel records of vpg.py:186-199 and log_performance (_functions.py:262-273)."""
+        B = float(B)
         world = self._world()
         if world > 1:
             s, B = self._reduce_logs(s, B, world)
@@ -393,7 +402,7 @@ class VPG(RLAlgorithm):
             tabular.record('/dLoss', vf_before - vf_after)
         with tabular.prefix('Evaluation/'):
             tabular.record('Iteration', itr)
-            tabular.record('NumEpisodes', f.n_eps)
+            tabular.record('NumEpisodes', n_eps)
             tabular.record('AverageDiscountedReturn', s[32])
             tabular.record('AverageReturn', s[33])
             tabular.record('StdReturn', s[34])
