@@ -355,7 +355,7 @@ class VPG(RLAlgorithm):
                 s = torch.segment_reduce(f.success.to(torch.float32), 'max', lengths=f.lengths)
             out[6] = s.to(torch.float64).mean()
         else:
-            out[6] = float('nan')
+            out[6:7].fill_(float('nan'))
         return und
 
     def _enqueue_iteration(self, eps):
