@@ -117,25 +117,44 @@ extern "C" int b2g_mlp_eval(int obs_dim, int hidden, int out_dim, const float* p
 // stats[s] = sum_b partial[b][P+s] in fp64.  With `params` given, applies
 // torch.optim.Adam's single-tensor update (make_optimizer, _functions.py:25-65;
 // amsgrad=False, weight_decay=0) in the same pass.
-__global__ void __launch_bounds__(256)
+constexpr int RED_PX = 32, RED_SL = 8;  // 32 parameters x 8 partial-row slices per block
+__global__ void __launch_bounds__(RED_PX * RED_SL)
 reduce_adam_kernel(const float* __restrict__ partial, int nb, int P, float scale,
                    float* __restrict__ grad_out, double* __restrict__ stats_out,
                    float* __restrict__ params, float* __restrict__ m, float* __restrict__ v,
                    const unsigned long long* __restrict__ step, double lr, double beta1,
                    double beta2, double eps) {
-    const int p = blockIdx.x * blockDim.x + threadIdx.x;
+    __shared__ double sh[RED_SL][RED_PX];
+    const int px = threadIdx.x & (RED_PX - 1), sl = threadIdx.x / RED_PX;
+    const int p = blockIdx.x * RED_PX + px;
     const int W = P + MLP_NSTATS;
-    if (p >= W) return;
-    if (p >= P) {
-        double s = 0.0;
-        for (int b = 0; b < nb; ++b) s += (double)partial[(int64_t)b * W + p];
-        if (stats_out) stats_out[p - P] = s;
+    const bool is_stat = p >= P;
+    // slice sl sums rows sl, sl+8, ...: a warp reads 32 consecutive floats of one row
+    float s = 0.0f;
+    double sd = 0.0;
+    if (p < W) {
+        if (is_stat) {
+            for (int b = sl; b < nb; b += RED_SL) sd += (double)partial[(int64_t)b * W + p];
+        } else {
+#pragma unroll 4
+            for (int b = sl; b < nb; b += RED_SL) s += partial[(int64_t)b * W + p];
+            sd = (double)s;
+        }
+    }
+    sh[sl][px] = sd;
+    __syncthreads();
+    if (sl != 0 || p >= W) return;
+    if (is_stat) {
+        double t = 0.0;
+#pragma unroll
+        for (int k = 0; k < RED_SL; ++k) t += sh[k][px];
+        if (stats_out) stats_out[p - P] = t;
         return;
     }
-    float s = 0.0f;
-#pragma unroll 8
-    for (int b = 0; b < nb; ++b) s += partial[(int64_t)b * W + p];
-    const float g = s * scale;
+    float sum = 0.0f;  // fixed order -> deterministic
+#pragma unroll
+    for (int k = 0; k < RED_SL; ++k) sum += (float)sh[k][px];
+    const float g = sum * scale;
     if (grad_out) grad_out[p] = g;
     if (params) {
         const double t = (double)(*step);
@@ -158,7 +177,7 @@ extern "C" int b2g_mlp_reduce(const float* ws_partial, int n_partials, int n_par
     B2G_CHECK_ARG(ws_partial && n_partials > 0 && n_params > 0, "bad arguments");
     B2G_CHECK_ARG(!params || (adam_m && adam_v && step_counter), "Adam needs m, v and the step counter");
     const int W = n_params + MLP_NSTATS;
-    reduce_adam_kernel<<<(W + 255) / 256, 256, 0, (cudaStream_t)stream>>>(
+    reduce_adam_kernel<<<(W + RED_PX - 1) / RED_PX, RED_PX * RED_SL, 0, (cudaStream_t)stream>>>(
         ws_partial, n_partials, n_params, scale, grad_out, stats_out, params, adam_m, adam_v,
         step_counter, lr, beta1, beta2, eps);
     B2G_CHECK_LAUNCH();

@@ -54,7 +54,7 @@ __device__ __forceinline__ float4 lds4(const float* p) { return *reinterpret_cas
 __device__ __forceinline__ void sts4(float* p, float4 v) { *reinterpret_cast<float4*>(p) = v; }
 
 template <int H, int O, int A, bool BWD>
-__global__ void __launch_bounds__(MLP_NT, 1) mlp_train_kernel(const MlpArgs a) {
+__global__ void __launch_bounds__(MLP_NT, 2) mlp_train_kernel(const MlpArgs a) {
     constexpr int R = MLP_R, RS = MLP_RS;
     constexpr int TXN = MlpSmem<H>::TXN, TYN = MlpSmem<H>::TYN, RPT = MlpSmem<H>::RPT,
                   KPT = MlpSmem<H>::KPT;

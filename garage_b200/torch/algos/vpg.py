@@ -361,15 +361,29 @@ class VPG(RLAlgorithm):
     def _enqueue_iteration(self, eps):
         """Everything of `_train_once` that runs on the device, without any host
         synchronisation (CUDA-graph capturable when the batch shape is static).
-        Returns (stats [40] float64 device tensor, B, n_eps)."""
+        Returns (stats [48] float64 device tensor, B, n_eps)."""
         f = self._prepare(eps)
-        stats = torch.zeros(40, dtype=torch.float64, device=f.obs.device)
+        stats = torch.zeros(48, dtype=torch.float64, device=f.obs.device)
+        pad_kl = self._pad_value_mode == 'reference' and f.fixed_len is None and self._log_stats
+        if pad_kl:
+            # the reference logs KL over the zero-PADDED observations too (vpg.py:172-173,
+            # 181-184): remember the old policy's mean at the all-zero observation
+            zero_obs = torch.zeros(1, f.obs.shape[1], device=f.obs.device)
+            old_mean0 = self.policy._module.mean(zero_obs)
         if self._log_stats:
             self._evaluate(f, stats[0:16])
         self._train(f)
         if self._log_stats:
             self._evaluate(f, stats[16:32])
         self._performance(f, stats[32:39])
+        if pad_kl:
+            dummy = torch.zeros(1, device=f.obs.device)
+            nb = ops.mlp_eval(self.policy.mlp_shape, self.policy.flat, zero_obs,
+                              act=torch.zeros(1, f.act.shape[1], device=f.obs.device), adv=dummy,
+                              old_logp=dummy, old_mean=old_mean0, old_log_std=f.old_log_std,
+                              **self._policy_kwargs())
+            ops.mlp_reduce(self.policy.mlp_shape, nb, 1.0, stats_out=stats[40:48])
+            stats[39:40].fill_(float(f.n_eps * int(self.max_episode_length) - f.B))  # padded entries
         return stats, f.B, f.n_eps
 
     def _train_once(self, itr, eps):
@@ -394,7 +408,8 @@ class VPG(RLAlgorithm):
             tabular.record('/LossAfter', pol_after)
             tabular.record('/dLoss', pol_before - pol_after)
             tabular.record('/KLBefore', s[1] / B)
-            tabular.record('/KL', s[17] / B)
+            # s[39] padded entries with KL s[41] each (pad_value_mode='reference' only)
+            tabular.record('/KL', (s[17] + s[39] * s[41]) / (B + s[39]))
             tabular.record('/Entropy', s[18] / B)
         with tabular.prefix(self._value_function.name):
             tabular.record('/LossBefore', vf_before)
@@ -418,7 +433,7 @@ class VPG(RLAlgorithm):
     def _reduce_logs(self, s, B, world):
         """Average the logging scalars over ranks (sums for the statistics)."""
         import torch.distributed as dist
-        t = torch.tensor(np.concatenate([s, [B]]), dtype=torch.float64, device=self.policy.flat.device)
+        t = torch.tensor(np.concatenate([s[:40], [B]]), dtype=torch.float64, device=self.policy.flat.device)
         perf = t[32:39].clone()
         dist.all_reduce(t, group=self._pg)
         t[32:39] = t[32:39] / world  # per-rank means -> mean of means (equal shard sizes)
@@ -426,7 +441,7 @@ class VPG(RLAlgorithm):
         dist.all_reduce(perf[4:5], op=dist.ReduceOp.MIN, group=self._pg)
         t[35], t[36] = perf[3], perf[4]
         out = t.cpu().numpy()
-        return out[:-1], float(out[-1])
+        return np.concatenate([out[:-1], s[40:]]), float(out[-1])
 
     def train(self, trainer):
         """Reference vpg.py:208-228."""

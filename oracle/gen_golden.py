@@ -1,0 +1,211 @@
+"""Generate tests/golden/*.npz by RUNNING the unmodified reference
+(/root/reference/src/garage, v2021.03.0) in the build container through the import
+shims of oracle/ref_shims.py.  Test infrastructure only.
+
+    python -m oracle.gen_golden          # rewrites tests/golden/
+
+The fixtures travel to the GPU box (the reference cannot) and pin both the oracle
+(tests/test_golden.py, CPU) and the CUDA path (tests/test_golden_gpu.py).
+"""
+import os
+import sys
+
+import numpy as np
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+OUT = os.path.join(ROOT, 'tests', 'golden')
+
+
+def flat_of(module_sd, prefix):
+    """state_dict -> garage_b200's flat order [log_std|W1|b1|W2|b2|W3|b3]."""
+    keys = ['_init_std', '_mean_module._layers.0.linear.weight', '_mean_module._layers.0.linear.bias',
+            '_mean_module._layers.1.linear.weight', '_mean_module._layers.1.linear.bias',
+            '_mean_module._output_layers.0.linear.weight', '_mean_module._output_layers.0.linear.bias']
+    return np.concatenate([module_sd[prefix + k].detach().numpy().reshape(-1) for k in keys]).astype(np.float32)
+
+
+def flat_grad_of(module, prefix):
+    named = dict(module.named_parameters())
+    keys = ['_init_std', '_mean_module._layers.0.linear.weight', '_mean_module._layers.0.linear.bias',
+            '_mean_module._layers.1.linear.weight', '_mean_module._layers.1.linear.bias',
+            '_mean_module._output_layers.0.linear.weight', '_mean_module._output_layers.0.linear.bias']
+    return np.concatenate([named[prefix + k].grad.numpy().reshape(-1) for k in keys]).astype(np.float32)
+
+
+def make_spec(obs_dim, act_dim, max_len):
+    import akro
+    from garage import EnvSpec
+    return EnvSpec(observation_space=akro.Box(low=-np.inf, high=np.inf, shape=(obs_dim, )),
+                   action_space=akro.Box(low=-1., high=1., shape=(act_dim, )),
+                   max_episode_length=max_len)
+
+
+def gen_gae():
+    from garage.np import discount_cumsum
+    from garage.torch import compute_advantages
+    rng = np.random.default_rng(0)
+    out = {}
+    for name, (N, P, g, l) in dict(a=(5, 50, 0.99, 0.95), b=(3, 200, 0.99, 0.97), c=(4, 33, 0.9, 1.0),
+                                   d=(2, 1000, 0.995, 0.9)).items():
+        b = rng.standard_normal((N, P)).astype(np.float32)
+        r = rng.standard_normal((N, P)).astype(np.float32)
+        adv = compute_advantages(g, l, P, torch.from_numpy(b), torch.from_numpy(r)).numpy()
+        ret = np.stack([discount_cumsum(row.astype(np.float64), g) for row in r])
+        out.update({name + '_baselines': b, name + '_rewards': r, name + '_adv': adv,
+                    name + '_ret': ret, name + '_cfg': np.array([g, l])})
+    np.savez_compressed(os.path.join(OUT, 'gae.npz'), **out)
+
+
+def gen_point_env():
+    from garage.envs import PointEnv
+    rng = np.random.default_rng(1)
+    out = {}
+    cfgs = dict(a=dict(goal=(1., 1.), max_episode_length=30),
+                b=dict(goal=(0.3, -0.2), done_bonus=7.5, max_episode_length=40),
+                c=dict(goal=(0.25, 0.25), never_done=True, max_episode_length=12))
+    for name, kw in cfgs.items():
+        env = PointEnv(**{k: (np.array(v, dtype=np.float32) if k == 'goal' else v) for k, v in kw.items()})
+        obs0, info = env.reset()
+        T = kw['max_episode_length']
+        goal = np.array(kw['goal'], np.float32)
+        acts, obs, rews, sts, succ = [], [obs0], [], [], []
+        for t in range(T):
+            # head towards the goal with noise so that some runs terminate early
+            a = (0.5 * (goal - obs[-1][:2]) + rng.standard_normal(2) * 0.08).astype(np.float32)
+            es = env.step(a)
+            acts.append(a); obs.append(es.observation); rews.append(es.reward)
+            sts.append(int(es.step_type)); succ.append(bool(es.env_info['success']))
+            if es.last:
+                break
+        out.update({name + '_actions': np.array(acts, np.float32), name + '_obs': np.array(obs, np.float32),
+                    name + '_rewards': np.array(rews, np.float64), name + '_step_types': np.array(sts, np.uint8),
+                    name + '_success': np.array(succ), name + '_params': np.array(
+                        [goal[0], goal[1], 5., kw.get('done_bonus', 0.), float(kw.get('never_done', False)),
+                         kw['max_episode_length']], np.float64)})
+    np.savez_compressed(os.path.join(OUT, 'point_env.npz'), **out)
+
+
+def gen_losses():
+    """PPO / VPG / value-function losses and per-parameter gradients from the reference's
+    own autograd graph (`_compute_loss_with_adv().backward()`, `compute_loss().backward()`),
+    then three Adam steps over fixed minibatch index lists."""
+    from garage.torch.algos import PPO, VPG
+    from garage.torch.policies import GaussianMLPPolicy
+    from garage.torch.value_functions import GaussianMLPValueFunction
+    out = {}
+    for k, (name, (O_, A, H, n)) in enumerate(dict(p64=(3, 1, 64, 600), p32=(3, 2, 32, 257),
+                                                   c64=(4, 1, 64, 300)).items()):
+        torch.manual_seed(100 + k)
+        rng = np.random.default_rng(200 + k)
+        spec = make_spec(O_, A, 200)
+        policy = GaussianMLPPolicy(spec, hidden_sizes=(H, H))
+        vf = GaussianMLPValueFunction(spec, hidden_sizes=(H, H))
+        # move away from the zero-bias init so every gradient path is exercised
+        with torch.no_grad():
+            for p in list(policy.parameters()) + list(vf.parameters()):
+                p.add_(torch.randn_like(p) * 0.1)
+        algo = PPO(spec, policy, vf, sampler=None)
+        vpg = VPG(spec, policy, vf, sampler=None)
+        # the old policy differs from the current one (ratio != 1, some rows clipped)
+        with torch.no_grad():
+            for p in algo._old_policy.parameters():
+                p.add_(torch.randn_like(p) * 0.05)
+        obs = torch.Tensor(rng.standard_normal((n, O_)))
+        act = torch.Tensor(rng.standard_normal((n, A)))
+        adv = torch.Tensor(rng.standard_normal(n))
+        ret = torch.Tensor(rng.standard_normal(n) * 3)
+        rew = torch.zeros(n)
+        with torch.no_grad():
+            old_ll = algo._old_policy(obs)[0].log_prob(act)
+        out[name + '_dims'] = np.array([O_, A, H, n])
+        out[name + '_policy_flat'] = flat_of(policy.state_dict(), '_module.')
+        out[name + '_vf_flat'] = flat_of(vf.state_dict(), 'module.')
+        out[name + '_obs'], out[name + '_act'] = obs.numpy(), act.numpy()
+        out[name + '_adv'], out[name + '_ret'], out[name + '_old_logp'] = adv.numpy(), ret.numpy(), old_ll.numpy()
+        for tag, al in (('ppo', algo), ('vpg', vpg)):
+            policy.zero_grad()
+            loss = al._compute_loss_with_adv(obs, act, rew, adv)
+            loss.backward()
+            out['{}_{}_loss'.format(name, tag)] = np.float64(loss.item())
+            out['{}_{}_grad'.format(name, tag)] = flat_grad_of(policy, '_module.')
+        vf.zero_grad()
+        loss = vf.compute_loss(obs, ret)
+        loss.backward()
+        out[name + '_vf_loss'] = np.float64(loss.item())
+        out[name + '_vf_grad'] = flat_grad_of(vf, 'module.')
+        with torch.no_grad():
+            new_dist, old_dist = policy(obs)[0], algo._old_policy(obs)[0]
+            out[name + '_kl'] = np.float64(torch.distributions.kl.kl_divergence(old_dist, new_dist).mean().item())
+            out[name + '_entropy'] = np.float64(new_dist.entropy().mean().item())
+            out[name + '_old_mean'] = old_dist.mean.numpy()
+            out[name + '_old_log_std'] = np.float64((old_dist.variance**.5).log().reshape(-1)[0].item())
+        # Adam: 3 PPO steps + 3 VF steps on fixed minibatches (lr of ppo.py:65-76)
+        idx = np.stack([rng.permutation(n)[:n // 2] for _ in range(3)]).astype(np.int32)
+        for mb in idx:
+            algo._train_policy(obs[mb], act[mb], rew[mb], adv[mb])
+            algo._train_value_function(obs[mb], ret[mb])
+        out[name + '_adam_idx'] = idx
+        out[name + '_policy_flat_after'] = flat_of(policy.state_dict(), '_module.')
+        out[name + '_vf_flat_after'] = flat_of(vf.state_dict(), 'module.')
+    np.savez_compressed(os.path.join(OUT, 'losses.npz'), **out)
+
+
+def gen_train_once():
+    """C1 end to end: reference LocalSampler (DefaultWorker) on PointEnv -> PPO._train_once."""
+    from garage.envs import PointEnv
+    from garage.experiment import deterministic
+    from garage.sampler import LocalSampler
+    from garage.torch.algos import PPO
+    from garage.torch.optimizers import OptimizerWrapper
+    from garage.torch.policies import GaussianMLPPolicy
+    from garage.torch.value_functions import GaussianMLPValueFunction
+    from oracle import ref_shims
+    out = {}
+    for name, (max_len, goal, nsamp) in dict(fixed=(25, (3., 3.), 500), early=(40, (0.35, 0.3), 600)).items():
+        import random
+        random.seed(7); np.random.seed(7); torch.manual_seed(7)  # deterministic.set_seed minus the TF call
+        env = PointEnv(goal=np.array(goal, dtype=np.float32), max_episode_length=max_len)
+        policy = GaussianMLPPolicy(env.spec, hidden_sizes=(32, 32))
+        vf = GaussianMLPValueFunction(env.spec, hidden_sizes=(32, 32))
+        sampler = LocalSampler(agents=policy, envs=env, max_episode_length=max_len, n_workers=2)
+        mk = lambda m: OptimizerWrapper((torch.optim.Adam, dict(lr=2.5e-4)), m,
+                                        max_optimization_epochs=3, minibatch_size=64)
+        algo = PPO(env.spec, policy, vf, sampler, policy_optimizer=mk(policy), vf_optimizer=mk(vf),
+                   gae_lambda=0.95)
+        eps = sampler.obtain_samples(0, nsamp, policy.get_param_values())
+        out[name + '_cfg'] = np.array([max_len, goal[0], goal[1]], np.float64)
+        out[name + '_policy_flat'] = flat_of(policy.state_dict(), '_module.')
+        out[name + '_vf_flat'] = flat_of(vf.state_dict(), 'module.')
+        out[name + '_obs'], out[name + '_act'] = eps.observations, eps.actions
+        out[name + '_rew'], out[name + '_lengths'] = eps.rewards, eps.lengths.astype(np.int64)
+        out[name + '_step_types'] = np.asarray(eps.step_types, dtype=np.uint8)
+        out[name + '_last_obs'] = eps.last_observations
+        out[name + '_success'] = eps.env_infos['success']
+        np.random.seed(11)  # the minibatch shuffles of BatchDataset
+        ref_shims.tabular.clear()
+        ret = algo._train_once(0, eps)
+        out[name + '_return'] = np.float64(ret)
+        out[name + '_policy_flat_after'] = flat_of(policy.state_dict(), '_module.')
+        out[name + '_vf_flat_after'] = flat_of(vf.state_dict(), 'module.')
+        keys = sorted(ref_shims.tabular.data)
+        out[name + '_log_keys'] = np.array(keys)
+        out[name + '_log_vals'] = np.array([float(ref_shims.tabular.data[k]) for k in keys])
+    np.savez_compressed(os.path.join(OUT, 'train_once.npz'), **out)
+
+
+def main():
+    from oracle import ref_shims
+    if not ref_shims.install():
+        sys.exit('/root/reference is not available here')
+    os.makedirs(OUT, exist_ok=True)
+    gen_gae()
+    gen_point_env()
+    gen_losses()
+    gen_train_once()
+    for f in sorted(os.listdir(OUT)):
+        print(f, os.path.getsize(os.path.join(OUT, f)))
+
+
+if __name__ == '__main__':
+    main()

@@ -301,6 +301,8 @@ class PPOPort:
     def train_once(self, batch, log=True):
         """vpg.py:136-206; returns the dict of dowel values."""
         obs, act, ret, adv, _ = self.prepare(batch)
+        # KL and entropy are logged over the PADDED observations (vpg.py:172-173, 181-184)
+        obs_p = torch.Tensor(O.pad_batch_array(batch['observations'], batch['lengths'], self.P))
         out = {}
         if log:
             with torch.no_grad():
@@ -321,9 +323,9 @@ class PPOPort:
             with torch.no_grad():
                 out['policy_loss_after'] = float(self.policy_loss(obs, act, adv))
                 out['vf_loss_after'] = float(self.vf_loss(obs, ret))
-                old, new = self.old_policy(obs), self.policy(obs)
+                old, new = self.old_policy(obs_p), self.policy(obs_p)
                 out['kl'] = float(torch.distributions.kl.kl_divergence(old, new).mean())
-                out['entropy'] = float(self.policy(obs).entropy().mean())
+                out['entropy'] = float(self.policy(obs_p).entropy().mean())
         self.old_policy.load_state_dict(self.policy.state_dict())
         starts = np.cumsum(batch['lengths']) - batch['lengths']
         und = np.add.reduceat(batch['rewards'], starts)

@@ -1,0 +1,114 @@
+"""Pin the oracle (oracle/np_oracle.py, oracle/port.py) against fixtures produced by
+RUNNING the unmodified reference (oracle/gen_golden.py -> tests/golden/*.npz).  No GPU."""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from oracle import np_oracle as O
+from oracle import port
+
+G = os.path.join(os.path.dirname(os.path.abspath(__file__)), 'golden')
+
+
+def load(name):
+    return np.load(os.path.join(G, name), allow_pickle=False)
+
+
+def rel(got, want):
+    return float(np.abs(np.asarray(got, np.float64) - want).max() / max(np.abs(want).max(), 1e-30))
+
+
+@pytest.mark.parametrize('case', 'abcd')
+def test_gae_and_returns(case):
+    d = load('gae.npz')
+    g, l = d[case + '_cfg']
+    b, r = d[case + '_baselines'], d[case + '_rewards']
+    adv = O.compute_advantages(g, l, b.shape[1], b, r)
+    assert np.allclose(adv, d[case + '_adv'], rtol=1e-5, atol=1e-5)
+    ret = O.discount_cumsum(r.astype(np.float64), g)
+    assert np.allclose(ret, d[case + '_ret'], rtol=1e-12, atol=1e-12)
+    # the time-major restatement gives the same numbers (each row = one episode ending at T-1)
+    st = np.full(b.T.shape, O.MID, np.uint8)
+    st[-1] = O.TIMEOUT
+    a2, r2 = O.gae_time_major(r.T.copy(), b.T.copy(), st, None, g, l)
+    assert np.allclose(a2.T, d[case + '_adv'], rtol=2e-5, atol=2e-5)
+    assert np.allclose(r2.T, d[case + '_ret'], rtol=1e-6, atol=1e-6)
+
+
+@pytest.mark.parametrize('case', 'abc')
+def test_point_env_transitions(case):
+    d = load('point_env.npz')
+    gx, gy, arena, bonus, never, max_len = d[case + '_params']
+    acts, obs = d[case + '_actions'], d[case + '_obs']
+    point, o0 = O.point_reset(1, (gx, gy))
+    assert np.array_equal(o0[0], obs[0])
+    for t, a in enumerate(acts):
+        point, o, rew, done, succ = O.point_step(point, a[None], goal=(gx, gy), arena_size=arena,
+                                                 done_bonus=bonus, never_done=bool(never))
+        assert np.allclose(o[0], obs[t + 1], rtol=1e-6, atol=1e-7)
+        assert abs(rew[0] - d[case + '_rewards'][t]) <= 1e-6 * max(1, abs(rew[0]))
+        assert bool(succ[0]) == bool(d[case + '_success'][t])
+        assert O.get_step_type(t + 1, int(max_len), bool(done[0])) == d[case + '_step_types'][t]
+
+
+@pytest.mark.parametrize('case', ['p64', 'p32', 'c64'])
+def test_losses_gradients_adam(case):
+    d = load('losses.npz')
+    O_, A, H, n = (int(v) for v in d[case + '_dims'])
+    obs, act, adv = d[case + '_obs'], d[case + '_act'], d[case + '_adv']
+    ret, olp = d[case + '_ret'], d[case + '_old_logp']
+    pf, vfl = d[case + '_policy_flat'], d[case + '_vf_flat']
+    for kind in ('ppo', 'vpg'):
+        loss, grad = O.policy_loss_and_grad(pf, O_, H, A, obs, act, adv, olp, kind=kind)
+        assert abs(loss - d['{}_{}_loss'.format(case, kind)]) <= 1e-5 * max(1, abs(loss))
+        want = d['{}_{}_grad'.format(case, kind)].astype(np.float64)
+        for k, v in O.unflatten_params(want, O_, H, A).items():
+            assert rel(O.unflatten_params(grad, O_, H, A)[k], v) < 1e-5, (kind, k)
+    loss, grad = O.vf_loss_and_grad(vfl, O_, H, obs, ret)
+    assert abs(loss - d[case + '_vf_loss']) <= 1e-5 * max(1, abs(loss))
+    want = d[case + '_vf_grad'].astype(np.float64)
+    for k, v in O.unflatten_params(want, O_, H, 1).items():
+        assert rel(O.unflatten_params(grad, O_, H, 1)[k], v) < 1e-5, k
+    # KL / entropy
+    p = O.unflatten_params(pf.astype(np.float64), O_, H, A)
+    mean, _, _ = O.mlp_forward(p, obs)
+    ls, _ = O.clamped_log_std(p)
+    kl = O.kl_normal(d[case + '_old_mean'].astype(np.float64), float(d[case + '_old_log_std']), mean, ls).mean()
+    assert abs(kl - d[case + '_kl']) <= 1e-4 * max(1e-3, abs(kl))
+    assert abs(O.normal_entropy(ls, A) - d[case + '_entropy']) < 1e-5
+    # Adam trajectory (policy and value function, 3 steps each)
+    p_, m, v = pf.copy(), np.zeros_like(pf), np.zeros_like(pf)
+    q_, mq, vq = vfl.copy(), np.zeros_like(vfl), np.zeros_like(vfl)
+    for it, mb in enumerate(d[case + '_adam_idx'], start=1):
+        _, g = O.policy_loss_and_grad(p_, O_, H, A, obs[mb], act[mb], adv[mb], olp[mb])
+        p_, m, v = O.adam_step(p_, g.astype(np.float32), m, v, it, lr=2.5e-4)
+        _, g = O.vf_loss_and_grad(q_, O_, H, obs[mb], ret[mb])
+        q_, mq, vq = O.adam_step(q_, g.astype(np.float32), mq, vq, it, lr=2.5e-4)
+    assert rel(p_ - pf, (d[case + '_policy_flat_after'] - pf).astype(np.float64)) < 5e-3
+    assert rel(q_ - vfl, (d[case + '_vf_flat_after'] - vfl).astype(np.float64)) < 5e-3
+
+
+@pytest.mark.parametrize('case', ['fixed', 'early'])
+def test_port_train_once_matches_reference(case):
+    """oracle/port.py (the CPU baseline) reproduces the reference's _train_once on the
+    reference's own batch: same minibatch shuffles (np.random.seed) -> same parameters."""
+    d = load('train_once.npz')
+    max_len = int(d[case + '_cfg'][0])
+    pol = port.GaussianMLP(3, 2, (32, 32))
+    vf = port.GaussianMLP(3, 1, (32, 32), min_std=None)
+    pol.load_flat(d[case + '_policy_flat'])
+    vf.load_flat(d[case + '_vf_flat'])
+    algo = port.PPOPort(pol, vf, max_len, kind='ppo', epochs=3, minibatch_size=64, gae_lambda=0.95)
+    batch = dict(observations=d[case + '_obs'], actions=d[case + '_act'], rewards=d[case + '_rew'],
+                 lengths=d[case + '_lengths'])
+    np.random.seed(11)
+    out = algo.train_once(batch)
+    assert np.allclose(pol.flat(), d[case + '_policy_flat_after'], rtol=1e-5, atol=1e-6)
+    assert np.allclose(vf.flat(), d[case + '_vf_flat_after'], rtol=1e-5, atol=1e-6)
+    logs = dict(zip(d[case + '_log_keys'], d[case + '_log_vals']))
+    assert abs(out['average_return'] - logs['Evaluation/AverageReturn']) < 1e-9
+    assert abs(out['policy_loss_after'] - logs['GaussianMLPPolicy/LossAfter']) < 1e-6
+    assert abs(out['vf_loss_after'] - logs['GaussianMLPValueFunction/LossAfter']) <= 1e-5 * abs(out['vf_loss_after'])
+    assert abs(out['kl'] - logs['GaussianMLPPolicy/KL']) < 1e-6
