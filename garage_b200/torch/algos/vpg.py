@@ -288,9 +288,7 @@ class VPG(RLAlgorithm):
         if opt.minibatch_size is None:
             return None
         if self._shuffle == 'numpy':
-            # BatchDataset: ids shuffled at construction and after each epoch (minibatch_dataset.py:14-35)
-            np.random.shuffle(host_ids)
-            return torch.from_numpy(host_ids.astype(np.int32)).to(self.policy.flat.device, non_blocking=True)
+            return torch.from_numpy(host_ids.astype(np.int32)).to(self.policy.flat.device)
         return ops.permutation(B, self._shuffle_seed, counter_dev=step_counter,
                                device=self.policy.flat.device)
 
@@ -305,7 +303,12 @@ class VPG(RLAlgorithm):
             import torch.distributed as dist
             mbs = max(1, mbs // world)  # minibatch_size is the global size
             grad = torch.empty(shape.P, dtype=torch.float32, device=flat.device)
-        host_ids = np.arange(B) if self._shuffle == 'numpy' else None
+        host_ids = None
+        if self._shuffle == 'numpy' and opt.minibatch_size is not None:
+            # BatchDataset: ids shuffled at construction and AFTER every epoch, the last one
+            # included (minibatch_dataset.py:14-35) -- same draws from numpy's global RNG
+            host_ids = np.arange(B)
+            np.random.shuffle(host_ids)
         kw = self._policy_kwargs() if policy else dict(loss_kind=ops.LOSS_VF)
         data = dict(act=f.act, adv=f.adv, old_logp=f.old_logp) if policy else dict(ret=f.ret)
         for _ in range(opt.max_optimization_epochs):
@@ -324,6 +327,8 @@ class VPG(RLAlgorithm):
                     ops.mlp_reduce(shape, nb, 1.0 / mb, params=flat, adam_m=m, adam_v=v,
                                    step_counter=step, lr=opt.lr, beta1=opt.beta1, beta2=opt.beta2,
                                    eps=opt.eps)
+            if host_ids is not None:
+                np.random.shuffle(host_ids)
 
     def _train(self, f):
         """vpg.py:230-248: all policy minibatches, then all value-function minibatches."""

@@ -88,7 +88,8 @@ def test_sampler_semantics_vecworker():
     from garage_b200.envs import PointEnv
     from garage_b200.sampler import LocalSampler
     from garage_b200.torch.policies import GaussianMLPPolicy
-    env = PointEnv(max_episode_length=16)
+    # goal out of reach within 16 steps: every episode ends by TIMEOUT (dynamic-shape path)
+    env = PointEnv(goal=np.array((3., 3.), dtype=np.float32), max_episode_length=16)
     pol = GaussianMLPPolicy(env.spec)
     s = LocalSampler(agents=pol, envs=env, max_episode_length=16, n_envs=8)
     eps = s.obtain_samples(0, 161, pol.get_param_values())
@@ -105,7 +106,7 @@ def test_sampler_semantics_vecworker():
     assert isinstance(host, EpisodeBatch) and len(host.split()) == 16
     # first observation of every episode is the reset observation (0, 0, |goal|)
     first = eps.observations[::16]
-    assert np.allclose(first, [[0, 0, math.sqrt(2)]] * 16)
+    assert np.allclose(first, [[0, 0, math.sqrt(18)]] * 16)
     # next_observations ends with last_observations
     assert np.array_equal(eps.next_observations[15], eps.last_observations[0])
     with pytest.raises(TypeError):
