@@ -1,0 +1,59 @@
+"""Host-side logic of the multi-GPU (env-sharded, data-parallel) path.
+
+Rank r of G owns envs [r*N/G, (r+1)*N/G) end to end (rollout, GAE, packing: no
+communication).  The exchanges are: one gradient all-reduce per minibatch step
+(NCCL, in VPG._run_minibatches), the global advantage moments (below), and the
+logging scalars once per iteration."""
+import torch
+import torch.distributed as dist
+
+
+def world_size(group=None):
+    if dist.is_available() and dist.is_initialized():
+        return dist.get_world_size(group)
+    return 1
+
+
+def combine_moments(stats, n, group=None):
+    """Global mean / unbiased variance / min from per-rank (mean, var, min) over n local
+    values each (Chan et al. parallel variance): one all_gather of 4 doubles.
+    `stats` is the double[3] tensor written by b2g_moments; works on any device/backend."""
+    world = world_size(group)
+    if world == 1:
+        return stats
+    mine = torch.stack([torch.tensor(float(n), dtype=torch.float64, device=stats.device),
+                        stats[0], stats[1] * (n - 1), stats[2]])
+    allv = [torch.empty_like(mine) for _ in range(world)]
+    dist.all_gather(allv, mine, group=group)
+    a = torch.stack(allv)
+    ntot = a[:, 0].sum()
+    mean = (a[:, 0] * a[:, 1]).sum() / ntot
+    m2 = (a[:, 2] + a[:, 0] * (a[:, 1] - mean)**2).sum()
+    return torch.stack([mean, m2 / (ntot - 1), a[:, 3].min()]).contiguous()
+
+
+def shard_envs(n_envs_total, rank, world):
+    """(n_envs on this rank, global id of its first env); the remainder goes to the
+    lowest ranks so that every env id in [0, n_envs_total) is owned exactly once."""
+    base, extra = divmod(int(n_envs_total), int(world))
+    n = base + (1 if rank < extra else 0)
+    off = rank * base + min(rank, extra)
+    return n, off
+
+
+def reduce_logs(s, B, group=None):
+    """Sum the loss/KL/entropy statistics and the sample count over ranks; average the
+    per-rank return means (equal shard sizes), max/min the extremes.  `s`: float64 tensor
+    [>=40] laid out like VPG._enqueue_iteration's stats; returns (s, B) tensors."""
+    world = world_size(group)
+    t = torch.cat([s[:40], torch.tensor([float(B)], dtype=torch.float64, device=s.device)])
+    if world == 1:
+        return t[:-1], t[-1]
+    perf = t[32:39].clone()
+    dist.all_reduce(t, group=group)
+    t[32:39] = t[32:39] / world
+    mx, mn = perf[3:4].clone(), perf[4:5].clone()
+    dist.all_reduce(mx, op=dist.ReduceOp.MAX, group=group)
+    dist.all_reduce(mn, op=dist.ReduceOp.MIN, group=group)
+    t[35], t[36] = mx[0], mn[0]
+    return t[:-1], t[-1]
