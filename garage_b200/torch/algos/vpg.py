@@ -426,413 +426,6 @@ class VPG(RLAlgorithm):
         return np.concatenate([red.cpu().numpy(), s[40:]]), float(Bt.item())
 
     def train(self, trainer):
-        raise NotImplementedError
-
-
-class _Flat:
-    """Episode-major packed training arrays on the device."""
-    # obs [B,O], act [B,A], rew/ret/adv/old_logp [B], old_mean [B,A], old_log_std: device
-    # float32[1], lengths [n_eps] int64, step_types [B] u8, success [B] u8|None, fixed_len int|None
-
-
-class VPG(RLAlgorithm):
-    """See the reference docstring (vpg.py:19-55) for the shared arguments.
-
-    Extra keyword-only arguments (all have defaults that keep the reference's behaviour):
-        shuffle (str): 'device' (counter-based Feistel permutation kernel) or 'numpy'
-            (np.random.shuffle on the host exactly like BatchDataset -- parity mode).
-        pad_value_mode (str): 'mask' cuts GAE at episode ends (what the reference's
-            docstring describes); 'reference' reproduces quirk Q5 (baselines evaluated on
-            zero-padded observations leak V(0) into early-terminated episodes).
-        process_group: torch.distributed group for the gradient all-reduce (default: the
-            world group when torch.distributed is initialised with world_size > 1).
-    """
-    _loss_kind = ops.LOSS_VPG
-    _clip = 0.0
-
-    def __init__(self, env_spec, policy, value_function, sampler, policy_optimizer=None,
-                 vf_optimizer=None, num_train_per_epoch=1, discount=0.99, gae_lambda=1,
-                 center_adv=True, positive_adv=False, policy_ent_coeff=0.0,
-                 use_softplus_entropy=False, stop_entropy_gradient=False,
-                 entropy_method='no_entropy', *, shuffle='device', pad_value_mode='mask',
-                 shuffle_seed=0, process_group=None, log_stats=True):
-        self._discount = discount
-        self.policy = policy
-        self.max_episode_length = env_spec.max_episode_length
-        self._value_function = value_function
-        self._gae_lambda = gae_lambda
-        self._center_adv = center_adv
-        self._positive_adv = positive_adv
-        self._policy_ent_coeff = policy_ent_coeff
-        self._use_softplus_entropy = use_softplus_entropy
-        self._stop_entropy_gradient = stop_entropy_gradient
-        self._entropy_method = entropy_method
-        self._n_samples = num_train_per_epoch
-        self._env_spec = env_spec
-        self._maximum_entropy = (entropy_method == 'max')
-        self._entropy_regularzied = (entropy_method == 'regularized')
-        self._check_entropy_configuration(entropy_method, center_adv, stop_entropy_gradient,
-                                          policy_ent_coeff)
-        self._episode_reward_mean = collections.deque(maxlen=100)
-        self._sampler = sampler
-        self._policy_optimizer = policy_optimizer or OptimizerWrapper(torch.optim.Adam, policy)
-        self._vf_optimizer = vf_optimizer or OptimizerWrapper(torch.optim.Adam, value_function)
-        if shuffle not in ('device', 'numpy'):
-            raise ValueError("shuffle must be 'device' or 'numpy'")
-        if pad_value_mode not in ('mask', 'reference'):
-            raise ValueError("pad_value_mode must be 'mask' or 'reference'")
-        self._shuffle = shuffle
-        self._shuffle_seed = int(shuffle_seed)
-        self._pad_value_mode = pad_value_mode
-        self._pg = process_group
-        self._log_stats = log_stats
-        self.last_stats = {}
-
-    @staticmethod
-    def _check_entropy_configuration(entropy_method, center_adv, stop_entropy_gradient,
-                                     policy_ent_coeff):
-        """Reference vpg.py:109-125 (same errors)."""
-        if entropy_method not in ('max', 'regularized', 'no_entropy'):
-            raise ValueError('Invalid entropy_method')
-        if entropy_method == 'max':
-            if center_adv:
-                raise ValueError('center_adv should be False when entropy_method is max')
-            if not stop_entropy_gradient:
-                raise ValueError('stop_gradient should be True when entropy_method is max')
-        if entropy_method == 'no_entropy':
-            if policy_ent_coeff != 0.0:
-                raise ValueError('policy_ent_coeff should be zero when there is no entropy method')
-
-    @property
-    def discount(self):
-        return self._discount
-
-    # ------------------------------------------------------------ distributed --
-    def _world(self):
-        return _dist.world_size(self._pg)
-
-    # ---------------------------------------------------------------- prepare --
-    def _entropy_value(self, log_std):
-        """Entropy of the (obs independent) Gaussian: sum_a 0.5 + 0.5 log 2pi + log std."""
-        A = self.policy.mlp_shape.A
-        ent = A * (0.5 + 0.5 * np.log(2 * np.pi)) + A * log_std
-        if self._use_softplus_entropy:
-            ent = torch.nn.functional.softplus(ent)
-        return ent
-
-    def _prepare(self, eps):
-        """EpisodeBatch -> flat device arrays with returns and (normalised) advantages."""
-        if isinstance(eps, DeviceEpisodeBatch) and eps.dev is not None:
-            return self._prepare_device(eps)
-        return self._prepare_host(eps)
-
-    def _prepare_device(self, eps):
-        dev, tm = eps.dev, eps.tm
-        f = _Flat()
-        T = eps.t_star + 1
-        N = tm.n
-        fixed = (eps.n_steps == T * N)  # every env contributed every row: no padding anywhere
-        vf = self._value_function
-        rew_tm = tm.rew[:T]
-        ls_dev = self._log_std_dev(eps, rew_tm.device)
-        if self._pad_value_mode == 'reference' and not fixed:
-            return self._prepare_padded(eps, dev, ls_dev, int(self.max_episode_length), True)
-        values = vf.module.mean(tm.obs[:T].reshape(T * N, -1)).reshape(T, N)
-        kw = dict(discount=self._discount, gae_lambda=self._gae_lambda)
-        if self._maximum_entropy:
-            # vpg.py:149-160: returns from the raw rewards, advantages from rewards + coeff * entropy
-            rew_ent = rew_tm + (self._policy_ent_coeff * self._entropy_value(ls_dev)).to(torch.float32)
-            adv_tm, _ = ops.gae_time_major(rew_ent, values, tm.step_type[:T], want_ret=False, **kw)
-            _, ret_tm = ops.gae_time_major(rew_tm, None, tm.step_type[:T], want_adv=False, **kw)
-        else:
-            adv_tm, ret_tm = ops.gae_time_major(rew_tm, values, tm.step_type[:T], **kw)
-        adv, ret = ops.pack_fields(tm.step_type, tm.ep_len, eps.ep_off, eps.t_star, eps.n_steps,
-                                   [adv_tm, ret_tm])
-        f.obs, f.act, f.rew, f.ret = dev.observations, dev.actions, dev.rewards, ret
-        f.old_logp, f.old_mean = dev.logp, dev.mean
-        f.old_log_std = ls_dev
-        f.B, f.lengths, f.n_eps = eps.n_steps, dev.lengths, eps.n_episodes
-        f.step_types, f.success = dev.step_types, dev.success
-        f.fixed_len = (eps.n_steps // eps.n_episodes) if fixed else None
-        f.adv = self._normalize(adv)
-        return f
-
-    @staticmethod
-    def _log_std_dev(eps, device):
-        ls = eps._log_std
-        if hasattr(ls, 'device_value'):
-            return ls.device_value
-        return torch.tensor([float(ls)], dtype=torch.float32, device=device)
-
-    def _prepare_padded(self, eps, dev, ls_dev, P, pad_with_v0):
-        """The reference's own data flow on padded [N,P] arrays (vpg.py:147-166).
-        pad_with_v0=True evaluates the value function on the zero-padded observations
-        too (quirk Q5); False leaves 0 beyond the end of each episode."""
-        lengths = dev.lengths
-        n_eps, B = eps.n_episodes, eps.n_steps
-        device = dev.observations.device
-        rows = torch.repeat_interleave(torch.arange(n_eps, device=device), lengths)
-        starts = torch.cumsum(lengths, 0) - lengths
-        cols = torch.arange(B, device=device) - torch.repeat_interleave(starts, lengths)
-        rew_p = torch.zeros(n_eps, P, device=device)
-        rew_p[rows, cols] = dev.rewards
-        vmod = self._value_function.module
-        if pad_with_v0:
-            obs_p = torch.zeros(n_eps, P, dev.observations.shape[1], device=device)
-            obs_p[rows, cols] = dev.observations
-            base_p = vmod.mean(obs_p.reshape(n_eps * P, -1)).reshape(n_eps, P)
-        else:
-            base_p = torch.zeros(n_eps, P, device=device)
-            base_p[rows, cols] = vmod.mean(dev.observations).reshape(-1)
-        kw = dict(discount=self._discount, gae_lambda=self._gae_lambda)
-        if self._maximum_entropy:
-            # the reference adds the entropy to EVERY padded entry (vpg.py:158-160)
-            rew_ent = rew_p + (self._policy_ent_coeff * self._entropy_value(ls_dev)).to(torch.float32)
-            if not pad_with_v0:
-                rew_ent = torch.zeros_like(rew_p).index_put_((rows, cols), rew_ent[rows, cols])
-            adv_p = ops.gae_episode_major(base_p, rew_ent.contiguous(), **kw)
-            _, ret_p = ops.gae_episode_major(base_p, rew_p, want_ret=True, **kw)
-        else:
-            adv_p, ret_p = ops.gae_episode_major(base_p, rew_p, want_ret=True, **kw)
-        f = _Flat()
-        f.obs, f.act, f.rew = dev.observations, dev.actions, dev.rewards
-        f.ret = ret_p[rows, cols].contiguous()
-        f.old_logp, f.old_mean, f.old_log_std = dev.logp, dev.mean, ls_dev
-        f.B, f.lengths, f.n_eps = B, lengths, n_eps
-        f.step_types, f.success, f.fixed_len = dev.step_types, dev.success, None
-        f.adv = self._normalize(adv_p[rows, cols].contiguous())
-        return f
-
-    def _prepare_host(self, eps):
-        """A host EpisodeBatch (e.g. made by the reference's sampler): upload, then the
-        padded data flow with libb2g kernels.  The old policy is the current policy at the
-        start of _train_once (vpg.py:107, 201; Q8)."""
-        device = self.policy.flat.device
-        n = len(eps.rewards)
-        dev = DeviceEpisodeBatch._Dev()
-        dev.observations = torch.as_tensor(np.asarray(eps.observations, np.float32), device=device).reshape(n, -1).contiguous()
-        dev.actions = torch.as_tensor(np.asarray(eps.actions, np.float32), device=device).reshape(n, -1).contiguous()
-        dev.rewards = torch.as_tensor(np.asarray(eps.rewards, np.float32), device=device).contiguous()
-        dev.lengths = torch.as_tensor(np.asarray(eps.lengths, dtype=np.int64), device=device)
-        dev.step_types = torch.as_tensor(np.asarray(eps.step_types, dtype=np.uint8), device=device)
-        succ = eps.env_infos.get('success') if hasattr(eps, 'env_infos') else None
-        dev.success = None if succ is None else torch.as_tensor(np.asarray(succ, np.uint8), device=device)
-        mod = self.policy._module
-        dev.mean = mod.mean(dev.observations)
-        ls = mod.log_std_value()
-        ls_dev = torch.tensor([ls], dtype=torch.float32, device=device)
-        dist = torch.distributions.Independent(
-            torch.distributions.Normal(dev.mean, float(np.exp(np.float32(ls)))), 1)
-        dev.logp = dist.log_prob(dev.actions).contiguous()
-        shim = type('E', (), {})()
-        shim.n_episodes, shim.n_steps = len(eps.lengths), n
-        if self._pad_value_mode == 'reference':
-            return self._prepare_padded(shim, dev, ls_dev, int(self.max_episode_length), True)
-        return self._prepare_padded(shim, dev, ls_dev, int(np.max(eps.lengths)), False)
-
-    def _normalize(self, adv):
-        """vpg.py:371-377 (variance, not std: quirk Q3); global statistics across ranks."""
-        if not (self._center_adv or self._positive_adv):
-            return adv
-        stats = ops.moments(adv)
-        if self._world() > 1:
-            stats = _dist.combine_moments(stats, adv.numel(), self._pg)
-        return ops.normalize_adv(adv, stats, self._center_adv, self._positive_adv)
-
-    # ------------------------------------------------------------ loss set-up --
-    def _flags(self):
-        fl = 0
-        if self._entropy_regularzied:
-            fl |= ops.FLAG_ENT_REG
-        if self._use_softplus_entropy:
-            fl |= ops.FLAG_SOFTPLUS_ENT
-        if self._stop_entropy_gradient:
-            fl |= ops.FLAG_STOP_ENT_GRAD
-        return fl
-
-    def _policy_kwargs(self):
-        mod = self.policy._module
-        return dict(loss_kind=self._loss_kind, flags=self._flags(), clip=self._clip,
-                    ent_coeff=self._policy_ent_coeff, min_log_std=mod.min_log_std,
-                    max_log_std=mod.max_log_std)
-
-    def _evaluate(self, f, out):
-        """The logging passes of vpg.py:168-173 / 178-184 in two forward launches:
-        out[0:8] policy statistics (loss, KL(old||new), entropy sums), out[8:16] value loss."""
-        pshape, vshape = self.policy.mlp_shape, self._value_function.mlp_shape
-        nb = ops.mlp_eval(pshape, self.policy.flat, f.obs, act=f.act, adv=f.adv,
-                          old_logp=f.old_logp, old_mean=f.old_mean, old_log_std=f.old_log_std,
-                          **self._policy_kwargs())
-        ops.mlp_reduce(pshape, nb, 1.0, stats_out=out[0:8])
-        nb = ops.mlp_eval(vshape, self._value_function.flat, f.obs, ret=f.ret, loss_kind=ops.LOSS_VF)
-        ops.mlp_reduce(vshape, nb, 1.0, stats_out=out[8:16])
-
-    # ------------------------------------------------------------------ train --
-    def _epoch_ids(self, B, opt, host_ids, step_counter):
-        if opt.minibatch_size is None:
-            return None
-        if self._shuffle == 'numpy':
-            return torch.from_numpy(host_ids.astype(np.int32)).to(self.policy.flat.device)
-        return ops.permutation(B, self._shuffle_seed, counter_dev=step_counter,
-                               device=self.policy.flat.device)
-
-    def _run_minibatches(self, opt, module_owner, f, policy):
-        """`for epoch: for minibatch: zero_grad; loss; backward; step` (vpg.py:244-293)."""
-        shape, flat = module_owner.mlp_shape, module_owner.flat
-        m, v, step = opt.state()
-        B = f.B
-        mbs = opt.minibatch_size or B
-        world = self._world()
-        if world > 1:
-            import torch.distributed as dist
-            mbs = max(1, mbs // world)  # minibatch_size is the global size
-            grad = torch.empty(shape.P, dtype=torch.float32, device=flat.device)
-        host_ids = None
-        if self._shuffle == 'numpy' and opt.minibatch_size is not None:
-            # BatchDataset: ids shuffled at construction and AFTER every epoch, the last one
-            # included (minibatch_dataset.py:14-35) -- same draws from numpy's global RNG
-            host_ids = np.arange(B)
-            np.random.shuffle(host_ids)
-        kw = self._policy_kwargs() if policy else dict(loss_kind=ops.LOSS_VF)
-        data = dict(act=f.act, adv=f.adv, old_logp=f.old_logp) if policy else dict(ret=f.ret)
-        for _ in range(opt.max_optimization_epochs):
-            idx = self._epoch_ids(B, opt, host_ids, step)
-            for start in range(0, B, mbs):
-                mb = min(mbs, B - start)
-                nb = ops.mlp_minibatch_grad(
-                    shape, flat, f.obs, idx=None if idx is None else idx[start:start + mb],
-                    start=start if idx is None else 0, mb=mb, step_counter=step, **data, **kw)
-                if world > 1:
-                    ops.mlp_reduce(shape, nb, 1.0, grad_out=grad)
-                    dist.all_reduce(grad, group=self._pg)
-                    ops.adam_step(flat, grad, 1.0 / (mb * world), m, v, step, opt.lr, opt.beta1,
-                                  opt.beta2, opt.eps)
-                else:
-                    ops.mlp_reduce(shape, nb, 1.0 / mb, params=flat, adam_m=m, adam_v=v,
-                                   step_counter=step, lr=opt.lr, beta1=opt.beta1, beta2=opt.beta2,
-                                   eps=opt.eps)
-            if host_ids is not None:
-                np.random.shuffle(host_ids)
-
-    def _train(self, f):
-        """vpg.py:230-248: all policy minibatches, then all value-function minibatches."""
-        self._run_minibatches(self._policy_optimizer, self.policy, f, policy=True)
-        self._run_minibatches(self._vf_optimizer, self._value_function, f, policy=False)
-
-    def _performance(self, f, out):
-        """log_performance (_functions.py:233-275) as device reductions: out[0:6] =
-        [mean discounted return, mean/std/max/min undiscounted return, termination rate],
-        out[6] = success rate (nan when the env reports no 'success')."""
-        n_eps = f.n_eps
-        if f.fixed_len:
-            und = f.rew.view(n_eps, f.fixed_len).sum(1, dtype=torch.float64)
-            first = torch.arange(0, f.B, f.fixed_len, device=f.rew.device)
-        else:
-            und = torch.segment_reduce(f.rew.to(torch.float64), 'sum', lengths=f.lengths)
-            first = torch.cumsum(f.lengths, 0) - f.lengths
-        last = (first + (f.fixed_len if f.fixed_len else f.lengths)) - 1
-        out[0] = f.ret[first].to(torch.float64).mean()
-        out[1] = und.mean()
-        out[2] = und.std(unbiased=False)
-        out[3] = und.max()
-        out[4] = und.min()
-        out[5] = (f.step_types[last] == int(StepType.TERMINAL)).to(torch.float64).mean()
-        if f.success is not None:
-            if f.fixed_len:
-                s = f.success.view(n_eps, f.fixed_len).max(1).values
-            else:
-                s = torch.segment_reduce(f.success.to(torch.float32), 'max', lengths=f.lengths)
-            out[6] = s.to(torch.float64).mean()
-        else:
-            out[6:7].fill_(float('nan'))
-        return und
-
-    def _enqueue_iteration(self, eps):
-        """Everything of `_train_once` that runs on the device, without any host
-        synchronisation (CUDA-graph capturable when the batch shape is static).
-        Returns (stats [48] float64 device tensor, B, n_eps)."""
-        f = self._prepare(eps)
-        stats = torch.zeros(48, dtype=torch.float64, device=f.obs.device)
-        pad_kl = self._pad_value_mode == 'reference' and f.fixed_len is None and self._log_stats
-        if pad_kl:
-            # the reference logs KL over the zero-PADDED observations too (vpg.py:172-173,
-            # 181-184): remember the old policy's mean at the all-zero observation
-            zero_obs = torch.zeros(1, f.obs.shape[1], device=f.obs.device)
-            old_mean0 = self.policy._module.mean(zero_obs)
-        if self._log_stats:
-            self._evaluate(f, stats[0:16])
-        self._train(f)
-        if self._log_stats:
-            self._evaluate(f, stats[16:32])
-        self._performance(f, stats[32:39])
-        if pad_kl:
-            dummy = torch.zeros(1, device=f.obs.device)
-            nb = ops.mlp_eval(self.policy.mlp_shape, self.policy.flat, zero_obs,
-                              act=torch.zeros(1, f.act.shape[1], device=f.obs.device), adv=dummy,
-                              old_logp=dummy, old_mean=old_mean0, old_log_std=f.old_log_std,
-                              **self._policy_kwargs())
-            ops.mlp_reduce(self.policy.mlp_shape, nb, 1.0, stats_out=stats[40:48])
-            stats[39:40].fill_(float(f.n_eps * int(self.max_episode_length) - f.B))  # padded entries
-        return stats, f.B, f.n_eps
-
-    def _train_once(self, itr, eps):
-        """One policy-optimisation iteration (reference vpg.py:136-206).
-
-        Returns:
-            numpy.float64: mean undiscounted return of the batch.
-        """
-        stats, B, n_eps = self._enqueue_iteration(eps)
-        return self._log_iteration(itr, stats.cpu().numpy(), B, n_eps)  # the single D2H read
-
-    def _log_iteration(self, itr, s, B, n_eps):
-        """The dowel records of vpg.py:186-199 and log_performance (_functions.py:262-273)."""
-        B = float(B)
-        world = self._world()
-        if world > 1:
-            s, B = self._reduce_logs(s, B, world)
-        pol_before, vf_before = s[0] / B, s[8] / B
-        pol_after, vf_after = s[16] / B, s[24] / B
-        with tabular.prefix(self.policy.name):
-            tabular.record('/LossBefore', pol_before)
-            tabular.record('/LossAfter', pol_after)
-            tabular.record('/dLoss', pol_before - pol_after)
-            tabular.record('/KLBefore', s[1] / B)
-            # s[39] padded entries with KL s[41] each (pad_value_mode='reference' only)
-            tabular.record('/KL', (s[17] + s[39] * s[41]) / (B + s[39]))
-            tabular.record('/Entropy', s[18] / B)
-        with tabular.prefix(self._value_function.name):
-            tabular.record('/LossBefore', vf_before)
-            tabular.record('/LossAfter', vf_after)
-            tabular.record('/dLoss', vf_before - vf_after)
-        with tabular.prefix('Evaluation/'):
-            tabular.record('Iteration', itr)
-            tabular.record('NumEpisodes', n_eps)
-            tabular.record('AverageDiscountedReturn', s[32])
-            tabular.record('AverageReturn', s[33])
-            tabular.record('StdReturn', s[34])
-            tabular.record('MaxReturn', s[35])
-            tabular.record('MinReturn', s[36])
-            tabular.record('TerminationRate', s[37])
-            if not np.isnan(s[38]):
-                tabular.record('SuccessRate', s[38])
-        self.last_stats = tabular.as_dict
-        self._episode_reward_mean.append(s[33])
-        return np.float64(s[33])
-
-    def _reduce_logs(self, s, B, world):
-        """Average the logging scalars over ranks (sums for the statistics)."""
-        import torch.distributed as dist
-        t = torch.tensor(np.concatenate([s[:40], [B]]), dtype=torch.float64, device=self.policy.flat.device)
-        perf = t[32:39].clone()
-        dist.all_reduce(t, group=self._pg)
-        t[32:39] = t[32:39] / world  # per-rank means -> mean of means (equal shard sizes)
-        dist.all_reduce(perf[3:4], op=dist.ReduceOp.MAX, group=self._pg)
-        dist.all_reduce(perf[4:5], op=dist.ReduceOp.MIN, group=self._pg)
-        t[35], t[36] = perf[3], perf[4]
-        out = t.cpu().numpy()
-        return np.concatenate([out[:-1], s[40:]]), float(out[-1])
-
-    def train(self, trainer):
         """Reference vpg.py:208-228."""
         last_return = None
         for _ in trainer.step_epochs():
