@@ -1,6 +1,7 @@
 // Host launchers for the fused MLP minibatch kernel, partial-gradient reduction,
 // Adam, and the forward-only evaluation paths.
-#include "mlp_train.cuh"
+#include "mlp_tc.cuh"
+#include <stdlib.h>
 
 // CTAs per launch: one per 128-row tile, capped at SMs x resident CTAs per SM
 // (persistent grid-stride over tiles beyond that).
@@ -36,6 +37,45 @@ static int launch_mlp(const MlpArgs& a, cudaStream_t s) {
     return B2G_OK;
 }
 
+// ---- tensor-core path (hidden 64): one CTA per SM, 128-row tiles
+static int g_mlp_path = -1;  // 0 auto (tcgen05 for hidden 64 backward), 1 CUDA-core fp32 only, 2 = 0
+static int mlp_path() {
+    if (g_mlp_path < 0) {
+        const char* e = getenv("B2G_MLP_PATH");
+        g_mlp_path = (e && (e[0] == 'f' || e[0] == '1')) ? 1 : 0;   // "ffma" / "1" forces the CUDA-core kernel
+    }
+    return g_mlp_path;
+}
+extern "C" int b2g_set_mlp_path(int path) {
+    B2G_CHECK_ARG(path >= 0 && path <= 2, "path must be 0 (auto), 1 (CUDA-core fp32) or 2 (tcgen05)");
+    g_mlp_path = path == 2 ? 0 : path;
+    return B2G_OK;
+}
+extern "C" int b2g_get_mlp_path(void) { return mlp_path(); }
+
+template <int H, int O, int A>
+constexpr bool mlp_has_tc() { return H == 64; }
+
+static int mlp_tc_grid(int64_t rows) {
+    const int64_t tiles = (rows + tc::R - 1) / tc::R;
+    const int64_t cap = 2 * (int64_t)b2g_sm_count();  // two CTAs per SM (smem and TMEM halves)
+    return (int)(tiles < cap ? (tiles > 0 ? tiles : 1) : cap);
+}
+
+template <int O, int A>
+static int launch_mlp_tc(const MlpArgs& a, cudaStream_t s) {
+    constexpr size_t smem = tc::smem_bytes<O, A>();
+    static bool configured = false;
+    if (!configured) {
+        B2G_CUDA(cudaFuncSetAttribute(tc::mlp_train_tc_kernel<O, A>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                      (int)smem));
+        configured = true;
+    }
+    tc::mlp_train_tc_kernel<O, A><<<mlp_tc_grid(a.mb), tc::NT, smem, s>>>(a);
+    B2G_CHECK_LAUNCH();
+    return B2G_OK;
+}
+
 #define B2G_MLP_SHAPES(X) X(64, 3, 1) X(64, 3, 2) X(64, 4, 1) X(32, 3, 1) X(32, 3, 2) X(32, 4, 1)
 
 static int mlp_unsupported(int O, int H, int A) {
@@ -46,8 +86,13 @@ static int mlp_unsupported(int O, int H, int A) {
 
 template <bool BWD>
 static int dispatch_mlp(int O, int H, int A, const MlpArgs& a, cudaStream_t s) {
-#define B2G_CASE(HH, OO, AA) \
-    if (H == HH && O == OO && A == AA) return launch_mlp<HH, OO, AA, BWD>(a, s);
+#define B2G_CASE(HH, OO, AA)                                                         \
+    if (H == HH && O == OO && A == AA) {                                             \
+        if constexpr (BWD && HH == 64) {                                             \
+            if (mlp_path() == 0) return launch_mlp_tc<OO, AA>(a, s);                 \
+        }                                                                            \
+        return launch_mlp<HH, OO, AA, BWD>(a, s);                                    \
+    }
     B2G_MLP_SHAPES(B2G_CASE)
 #undef B2G_CASE
     return mlp_unsupported(O, H, A);
@@ -56,9 +101,11 @@ static int dispatch_mlp(int O, int H, int A, const MlpArgs& a, cudaStream_t s) {
 // number of per-CTA partial rows a launch over `rows` rows writes (<0: unsupported shape)
 extern "C" int b2g_mlp_num_partials(int obs_dim, int hidden, int out_dim, int backward,
                                     int64_t rows) {
-#define B2G_CASE(HH, OO, AA)                                               \
-    if (hidden == HH && obs_dim == OO && out_dim == AA)                    \
-        return backward ? mlp_grid<HH, OO, AA, true>(rows) : mlp_grid<HH, OO, AA, false>(rows);
+#define B2G_CASE(HH, OO, AA)                                                                   \
+    if (hidden == HH && obs_dim == OO && out_dim == AA) {                                      \
+        if (backward && HH == 64 && mlp_path() == 0) return mlp_tc_grid(rows);                 \
+        return backward ? mlp_grid<HH, OO, AA, true>(rows) : mlp_grid<HH, OO, AA, false>(rows); \
+    }
     B2G_MLP_SHAPES(B2G_CASE)
 #undef B2G_CASE
     return mlp_unsupported(obs_dim, hidden, out_dim);

@@ -1,0 +1,620 @@
+// Tensor-core (tcgen05, kind::tf32, 3xTF32 split) form of the fused minibatch kernel of
+// mlp_train.cuh for hidden = (64, 64): same inputs, same per-CTA partial output, same
+// per-row loss code (mlp_row_loss) -- only the three H x H contractions, the bias/W1
+// gradient column sums and their staging differ.  Replaces the same reference code:
+// torch/algos/vpg.py:250-293, ppo.py:96-132, vpg.py:324-347,408-455,
+// value_functions/gaussian_mlp_value_function.py:81-97 and the autograd graph of
+// torch/modules/multi_headed_mlp_module.py:136-151.
+//
+// Shape of the launch: 64-row tiles, 256 threads, ~110 KB of shared memory and 256 TMEM
+// columns per CTA, so TWO CTAs are resident per SM: while one waits for its MMAs the other
+// runs its CUDA-core stage (tanh, loss, splits), which is how the serial per-tile chain
+// L1 -> GEMM1 -> EPI1 -> GEMM2|GEMM3 -> EPI2 -> GEMM4 keeps both pipes busy.
+//
+// Data layout in shared memory: every operand is a stack of "panels"
+//   panel = [rows][32 floats = 128 B], the four 32-byte chunks of a row XOR-swizzled by row%4
+// (UMMA descriptor layout_type 1: 128-byte swizzle with 32-byte atoms).  The SAME bytes are a
+// K-major operand (M/N = row, K = feature; SBO = 512, +32 B per K=8 step) and an MN-major
+// operand (M/N = feature, K = row; LBO = panel stride, SBO = 512, +1024 B per K=8 step), so the
+// activations are written once and feed both the forward/input-gradient GEMMs (contraction over
+// features) and the weight-gradient GEMMs (contraction over rows).  Verified on B200 by
+// tools/umma_probe.cu (`panel` cases G1-G4).
+//
+// Per 64-row tile (fp32 = hi + lo, hi = tf32 round-to-nearest, lo = x - hi; products hi*hi +
+// lo*hi + hi*lo accumulate in fp32 in TMEM):
+//   L1 (CUDA cores)  h1 = tanh(W1 x + b1)                       -> ACT panels hi0 hi1 | aug | lo0 lo1
+//   GEMM1  D[r][c]  = sum_k h1[r][k] W2[c][k]        M64 N64    A=ACT (K-major)  B=W (K-major)
+//   EPI1   h2 = tanh(D + b2); mu = W3 h2 + b3; loss; dz2        -> DZ panels hi0 hi1 lo0 lo1
+//   GEMM2  D[r][k]  = sum_c dz2[r][c] W2[c][k]       M64 N64    A=DZ (K-major)   B=W (MN-major)
+//   GEMM3  G[m][n] += sum_r dz2{hi|lo}[r][m] [h1|1|x][r][n]   M128(hi;lo stacked) N72/64, MN/MN
+//   EPI2   dz1 = D (1 - h1^2)                                   -> DZ panels (after GEMM3 drained)
+//   GEMM4  F[m][n] += sum_r dz1{hi|lo}[r][m] [1|x][r][n]       M128 N8, MN/MN
+// dW2 = G[0:64, 0:64] + G[64:128, 0:64], db2 = G[:, 64], db1 = F[:, 0], dW1 = F[:, 1:1+O];
+// dW3 accumulates in registers, db3 / dlog_std / statistics are row sums as in mlp_train.cuh.
+// The M=64 accumulator D lives in TMEM lanes (m%16) + 32*(m/16); the epilogues read it with
+// tcgen05.ld.16x256b (thread t of warp q: rows 16q + t/4 and +8, column pairs 8i + 2(t%4)),
+// so all 32 lanes of every warp carry data.
+#pragma once
+#include "mlp_train.cuh"
+
+namespace tc {
+constexpr int R = 64, NT = 256, H = 64;
+constexpr uint32_t PANEL = R * 128, WPANEL = H * 128;
+constexpr uint32_t OFF_ACT = 0;                      // 5 panels: hi0 hi1 aug lo0 lo1
+constexpr uint32_t OFF_DZ = OFF_ACT + 5 * PANEL;     // 4 panels: hi0 hi1 lo0 lo1
+constexpr uint32_t OFF_W = OFF_DZ + 4 * PANEL;       // 4 weight panels: hi0 hi1 lo0 lo1
+constexpr uint32_t OFF_SMALL = OFF_W + 4 * WPANEL;   // 106,496
+constexpr uint32_t TM_D = 0, TM_G = 64, TM_F = 136;
+
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+// shared-memory matrix descriptor: layout_type 1 (128B swizzle, 32B atoms), version 1
+__device__ __forceinline__ uint64_t umma_desc(uint32_t saddr, uint32_t lbo, uint32_t sbo) {
+    return (uint64_t)((saddr >> 4) & 0x3FFFu) | ((uint64_t)((lbo >> 4) & 0x3FFFu) << 16) |
+           ((uint64_t)((sbo >> 4) & 0x3FFFu) << 32) | (1ull << 46) | (1ull << 61);
+}
+// instruction descriptor, kind::tf32, fp32 accumulate
+__host__ __device__ constexpr uint32_t umma_idesc(int M, int N, int a_mn, int b_mn) {
+    return (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)a_mn << 15) | ((uint32_t)b_mn << 16) |
+           ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
+}
+__device__ __forceinline__ void umma_tf32(uint32_t d_tmem, uint64_t da, uint64_t db, uint32_t idesc, uint32_t acc) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t}\n" ::"r"(d_tmem),
+        "l"(da), "l"(db), "r"(idesc), "r"(acc)
+        : "memory");
+}
+__device__ __forceinline__ void umma_commit(uint32_t bar) {
+    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ void fence_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+__device__ __forceinline__ void tc_before_sync() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_after_sync() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+
+// bounded spin: a lost MMA completion must surface as an error, not as a hung GPU
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
+    uint32_t done = 0;
+    for (uint32_t spin = 0; !done; ++spin) {
+        asm volatile(
+            "{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+            "selp.u32 %0, 1, 0, p;\n\t}\n"
+            : "=r"(done)
+            : "r"(bar), "r"(parity)
+            : "memory");
+        if (spin > (1u << 24)) __trap();
+    }
+}
+
+// M=64 accumulator fragment: 16 lanes x 32 columns -> v[4i+0,1] = (row g, cols 8i+2p,+1),
+// v[4i+2,3] = (row g+8, same cols); g = lane/4, p = lane%4
+__device__ __forceinline__ void tmem_ld_frag(uint32_t taddr, float (&v)[16]) {
+    uint32_t u[16];
+    asm volatile(
+        "tcgen05.ld.sync.aligned.16x256b.x4.b32 "
+        "{%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15}, [%16];"
+        : "=r"(u[0]), "=r"(u[1]), "=r"(u[2]), "=r"(u[3]), "=r"(u[4]), "=r"(u[5]), "=r"(u[6]), "=r"(u[7]),
+          "=r"(u[8]), "=r"(u[9]), "=r"(u[10]), "=r"(u[11]), "=r"(u[12]), "=r"(u[13]), "=r"(u[14]), "=r"(u[15])
+        : "r"(taddr)
+        : "memory");
+    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+#pragma unroll
+    for (int i = 0; i < 16; ++i) v[i] = __uint_as_float(u[i]);
+}
+// 16 consecutive fp32 columns of this thread's TMEM lane (warp w reads lanes 32*(w%4)..+31)
+__device__ __forceinline__ void tmem_ld16(uint32_t taddr, float (&v)[16]) {
+    uint32_t u[16];
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x16.b32 "
+        "{%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15}, [%16];"
+        : "=r"(u[0]), "=r"(u[1]), "=r"(u[2]), "=r"(u[3]), "=r"(u[4]), "=r"(u[5]), "=r"(u[6]), "=r"(u[7]),
+          "=r"(u[8]), "=r"(u[9]), "=r"(u[10]), "=r"(u[11]), "=r"(u[12]), "=r"(u[13]), "=r"(u[14]), "=r"(u[15])
+        : "r"(taddr)
+        : "memory");
+    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+#pragma unroll
+    for (int i = 0; i < 16; ++i) v[i] = __uint_as_float(u[i]);
+}
+
+// tanh x = 1 - 2 / (1 + e^{2x}) with the SFU's ex2 / rcp: absolute error ~2e-7 (|tanh| <= 1),
+// a quarter of tanhf's instruction count; saturates correctly (e -> inf: 1, e -> 0: -1)
+__device__ __forceinline__ float tanh_sfu(float x) {
+    float e, r;
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e) : "f"(x * 2.8853900817779268f));
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(e + 1.0f));
+    return fmaf(-2.0f, r, 1.0f);
+}
+#ifdef B2G_TC_PRECISE_TANH
+#define TC_TANH(x) tanhf(x)
+#else
+#define TC_TANH(x) tanh_sfu(x)
+#endif
+
+// fp32 -> (tf32 round-to-nearest, exact remainder)
+__device__ __forceinline__ void split_tf32(float x, float& hi, float& lo) {
+    uint32_t u;
+    asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(u) : "f"(x));
+    hi = __uint_as_float(u);
+    lo = x - hi;
+}
+// byte offset of the 16-byte chunk j (features 4j..4j+3 of the panel) of `row`
+__device__ __forceinline__ uint32_t chunk_off(int row, int j) {
+    return (uint32_t)row * 128u + ((((uint32_t)(j >> 1) ^ (uint32_t)row) & 3u) << 5) + ((uint32_t)(j & 1) << 4);
+}
+// byte offset of the feature pair (8i + 2p, +1) of `row` (fragment layout of tmem_ld_frag)
+__device__ __forceinline__ uint32_t pair_off(int row, int i, int p) {
+    return (uint32_t)row * 128u + ((((uint32_t)i ^ (uint32_t)row) & 3u) << 5) + (uint32_t)p * 8u;
+}
+__device__ __forceinline__ void store_split4(uint8_t* hi_panel, uint8_t* lo_panel, uint32_t off, const float* v) {
+    float4 h, l;
+    split_tf32(v[0], h.x, l.x); split_tf32(v[1], h.y, l.y);
+    split_tf32(v[2], h.z, l.z); split_tf32(v[3], h.w, l.w);
+    *reinterpret_cast<float4*>(hi_panel + off) = h;
+    *reinterpret_cast<float4*>(lo_panel + off) = l;
+}
+__device__ __forceinline__ void store_split2(uint8_t* hi_panel, uint8_t* lo_panel, uint32_t off, float v0, float v1) {
+    float2 h, l;
+    split_tf32(v0, h.x, l.x); split_tf32(v1, h.y, l.y);
+    *reinterpret_cast<float2*>(hi_panel + off) = h;
+    *reinterpret_cast<float2*>(lo_panel + off) = l;
+}
+
+// ---- MMA issue sequences (one thread) ----
+__device__ __forceinline__ void issue_gemm1(uint32_t sb, uint32_t tmem) {
+    constexpr uint32_t ID = umma_idesc(64, 64, 0, 0);
+#pragma unroll
+    for (int pass = 0; pass < 3; ++pass) {
+        const uint32_t ao = OFF_ACT + (pass == 1 ? 3 * PANEL : 0), bo = OFF_W + (pass == 2 ? 2 * WPANEL : 0);
+#pragma unroll
+        for (int ks = 0; ks < 8; ++ks)
+            umma_tf32(tmem + TM_D, umma_desc(sb + ao + (ks >> 2) * PANEL + (ks & 3) * 32, 1024, 512),
+                      umma_desc(sb + bo + (ks >> 2) * WPANEL + (ks & 3) * 32, 1024, 512), ID, (pass | ks) != 0);
+    }
+}
+__device__ __forceinline__ void issue_gemm2(uint32_t sb, uint32_t tmem) {
+    constexpr uint32_t ID = umma_idesc(64, 64, 0, 1);
+#pragma unroll
+    for (int pass = 0; pass < 3; ++pass) {
+        const uint32_t ao = OFF_DZ + (pass == 1 ? 2 * PANEL : 0), bo = OFF_W + (pass == 2 ? 2 * WPANEL : 0);
+#pragma unroll
+        for (int ks = 0; ks < 8; ++ks)
+            umma_tf32(tmem + TM_D, umma_desc(sb + ao + (ks >> 2) * PANEL + (ks & 3) * 32, 1024, 512),
+                      umma_desc(sb + bo + ks * 1024, WPANEL, 512), ID, (pass | ks) != 0);
+    }
+}
+// nks = ceil(valid rows / 8): rows past the minibatch contribute nothing and are skipped
+__device__ __forceinline__ void issue_gemm3(uint32_t sb, uint32_t tmem, bool first, int nks) {
+    constexpr uint32_t ID72 = umma_idesc(128, 72, 1, 1), ID64 = umma_idesc(128, 64, 1, 1);
+#pragma unroll
+    for (int ks = 0; ks < R / 8; ++ks)
+        if (ks < nks)
+            umma_tf32(tmem + TM_G, umma_desc(sb + OFF_DZ + ks * 1024, PANEL, 512),
+                      umma_desc(sb + OFF_ACT + ks * 1024, PANEL, 512), ID72, !(first && ks == 0));
+#pragma unroll
+    for (int ks = 0; ks < R / 8; ++ks)
+        if (ks < nks)
+            umma_tf32(tmem + TM_G, umma_desc(sb + OFF_DZ + ks * 1024, PANEL, 512),
+                      umma_desc(sb + OFF_ACT + 3 * PANEL + ks * 1024, PANEL, 512), ID64, 1);
+}
+__device__ __forceinline__ void issue_gemm4(uint32_t sb, uint32_t tmem, bool first, int nks) {
+    constexpr uint32_t ID8 = umma_idesc(128, 8, 1, 1);
+#pragma unroll
+    for (int pass = 0; pass < 2; ++pass)
+#pragma unroll
+        for (int ks = 0; ks < R / 8; ++ks)
+            if (ks < nks)
+                umma_tf32(tmem + TM_F, umma_desc(sb + OFF_DZ + ks * 1024, PANEL, 512),
+                          umma_desc(sb + OFF_ACT + 2 * PANEL + pass * 32 + ks * 1024, PANEL, 512), ID8,
+                          !(first && pass == 0 && ks == 0));
+}
+
+template <int O, int A>
+struct Small {  // float offsets inside the small region
+    static constexpr int NIN = A + 3;  // act[A], adv, old_logp, ret
+    static constexpr int W1 = 0, B1 = W1 + H * O, B2 = B1 + H, W3 = B2 + H, B3 = W3 + A * H,
+                         X = B3 + 4, MU = X + R * 4, IN = MU + 2 * A * R, SRC = IN + R * NIN + (R * NIN) % 2,
+                         BARS = SRC + 2 * R /* int64[R] */, TSLOT = BARS + 8 /* 4 x u64 */, END = TSLOT + 4;
+};
+template <int O, int A>
+constexpr size_t smem_bytes() { return OFF_SMALL + sizeof(float) * Small<O, A>::END; }
+
+// minibatch row id of (tile, row) or -1 past the end
+__device__ __forceinline__ int64_t tile_src(const MlpArgs& a, int64_t tile, int64_t ntiles, int r) {
+    if (tile >= ntiles) return -1;
+    const int64_t m = tile * R + r;
+    if (m >= a.mb) return -1;
+    return a.idx ? (int64_t)a.idx[m] : (a.start + m);
+}
+
+template <int O, int A>
+struct RowData {  // what the gather stage loads per row
+    float x[4];
+    float in[A + 3];
+};
+template <int O, int A>
+__device__ __forceinline__ RowData<O, A> load_row(const MlpArgs& a, int64_t src) {
+    RowData<O, A> d;
+#pragma unroll
+    for (int o = 0; o < 4; ++o) d.x[o] = 0.0f;
+#pragma unroll
+    for (int i = 0; i < A + 3; ++i) d.in[i] = 0.0f;
+    if (src >= 0) {
+#pragma unroll
+        for (int o = 0; o < O; ++o) d.x[o] = a.obs[src * O + o];
+        if (a.loss_kind == LOSS_VF) {
+            d.in[A + 2] = a.ret[src];
+        } else {
+#pragma unroll
+            for (int q = 0; q < A; ++q) d.in[q] = a.act[src * A + q];
+            d.in[A] = a.adv[src];
+            if (a.loss_kind == LOSS_PPO) d.in[A + 1] = a.old_logp[src];
+        }
+    }
+    return d;
+}
+
+template <int O, int A>
+__global__ void __launch_bounds__(NT, 2) mlp_train_tc_kernel(const MlpArgs a) {
+    static_assert(O <= 4 && A <= 4, "aug panel holds [1 | x] in 8 columns; obs staged as float4");
+    using S = Small<O, A>;
+    constexpr int NIN = S::NIN;
+    const MlpLayout L{O, H, A};
+    const int P = L.total();
+    extern __shared__ __align__(1024) uint8_t smem[];
+    float* sm = reinterpret_cast<float*>(smem + OFF_SMALL);
+    float *sW1 = sm + S::W1, *sB1 = sm + S::B1, *sB2 = sm + S::B2, *sW3 = sm + S::W3, *sB3 = sm + S::B3,
+          *sX = sm + S::X, *sMu = sm + S::MU, *sIn = sm + S::IN;
+    int64_t* sSrc = reinterpret_cast<int64_t*>(sm + S::SRC);
+    uint32_t* tslot = reinterpret_cast<uint32_t*>(sm + S::TSLOT);
+    const uint32_t sb = smem_u32(smem);
+    const uint32_t bar1 = smem_u32(sm + S::BARS), bar2 = bar1 + 8, bar3 = bar1 + 16, bar4 = bar1 + 24;
+    const int tid = threadIdx.x, w = tid >> 5, l = tid & 31;
+    const int64_t ntiles = (a.mb + R - 1) / R;
+
+    // ---- gather pipeline (threads 0..R-1 own one row): row ids run two tiles ahead of the
+    // tile being computed, row data one tile ahead, so no stage waits on a dependent load
+    int64_t src_n = -1, src_nn = -1;
+    RowData<O, A> row_n;
+    if (tid < R) {
+        src_n = tile_src(a, blockIdx.x, ntiles, tid);
+        src_nn = tile_src(a, (int64_t)blockIdx.x + gridDim.x, ntiles, tid);
+        row_n = load_row<O, A>(a, src_n);
+    }
+
+    // ---- one-time setup: barriers, TMEM, weights (W2 as hi/lo panels, the rest fp32)
+    if (tid == 0) {
+        if (sb & 1023u) __trap();
+#pragma unroll
+        for (int i = 0; i < 4; ++i) asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(bar1 + 8 * i));
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (w == 1) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], 256;" ::"r"(smem_u32(tslot)) : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    {
+        const float* w2 = a.params + L.off_w2();  // 4-byte aligned only (offset 1 + H*O + H floats)
+        float v[4][4];
+#pragma unroll
+        for (int i = 0; i < 4; ++i)
+#pragma unroll
+            for (int j = 0; j < 4; ++j) v[i][j] = __ldg(w2 + (tid + NT * i) * 4 + j);
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            const int e = (tid + NT * i) * 4, c = e >> 6, k = e & 63;
+            const uint32_t off = (uint32_t)(k >> 5) * WPANEL + chunk_off(c, (k & 31) >> 2);
+            store_split4(smem + OFF_W, smem + OFF_W + 2 * WPANEL, off, v[i]);
+        }
+    }
+    for (int i = tid; i < H * O; i += NT) sW1[i] = a.params[L.off_w1() + i];
+    if (tid < H) {
+        sB1[tid] = a.params[L.off_b1() + tid];
+        sB2[tid] = a.params[L.off_b2() + tid];
+    }
+    for (int i = tid; i < A * H; i += NT) sW3[i] = a.params[L.off_w3() + i];
+    if (tid < A) sB3[tid] = a.params[L.off_b3() + tid];
+    const MlpDist dist = mlp_dist(a, a.params[L.off_logstd()]);
+    if (a.step_counter && blockIdx.x == 0 && tid == 0) *a.step_counter += 1ull;
+    fence_async_smem();
+    tc_before_sync();
+    __syncthreads();
+    tc_after_sync();
+    const uint32_t tmem = *tslot;
+
+    // ---- epilogue role: rows ra = 16q + g and rb = ra + 8, feature pairs 32hf + 8i + 2p (+1)
+    const int q4 = w & 3, hf = w >> 2, g = l >> 2, p = l & 3;
+    const int ra = 16 * q4 + g, rb = ra + 8, c0 = 32 * hf;
+    const uint32_t tfrag = tmem + ((uint32_t)(32 * q4) << 16) + TM_D + c0;
+    float gW3[A][8], gB3[A];
+    MlpRowAcc racc{};
+#pragma unroll
+    for (int q = 0; q < A; ++q) {
+        gB3[q] = 0.0f;
+#pragma unroll
+        for (int c = 0; c < 8; ++c) gW3[q][c] = 0.0f;
+    }
+    uint8_t* const act_hi = smem + OFF_ACT + hf * PANEL;
+    uint8_t* const act_lo = smem + OFF_ACT + (3 + hf) * PANEL;
+    uint8_t* const dz_hi = smem + OFF_DZ + hf * PANEL;
+    uint8_t* const dz_lo = smem + OFF_DZ + (2 + hf) * PANEL;
+    float w3c[A][8], b2c[8];  // this thread's columns of W3 and b2
+#pragma unroll
+    for (int i = 0; i < 4; ++i)
+#pragma unroll
+        for (int e = 0; e < 2; ++e) {
+            const int c = c0 + 8 * i + 2 * p + e;
+            b2c[2 * i + e] = sB2[c];
+#pragma unroll
+            for (int q = 0; q < A; ++q) w3c[q][2 * i + e] = sW3[q * H + c];
+        }
+
+    uint32_t it = 0;
+    for (int64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++it) {
+        const uint32_t par = it & 1;
+        const int64_t m0 = tile * R;
+        const int valid = (int)((a.mb - m0) < R ? (a.mb - m0) : R);
+        const int nks = (valid + 7) >> 3;
+        if (it > 0) mbar_wait(bar4, par ^ 1);  // every MMA of the previous tile has drained
+        // ---- publish this tile's rows; aug panel row = [1 x_hi 0.. | 0 x_lo 0..]; prefetch ahead
+        if (tid < R) {
+            sSrc[tid] = src_n;
+            float xh[8], xl[8];
+#pragma unroll
+            for (int i = 0; i < 8; ++i) { xh[i] = 0.0f; xl[i] = 0.0f; }
+            xh[0] = 1.0f;
+#pragma unroll
+            for (int o = 0; o < O; ++o) split_tf32(row_n.x[o], xh[1 + o], xl[1 + o]);
+            *reinterpret_cast<float4*>(sX + tid * 4) = make_float4(row_n.x[0], row_n.x[1], row_n.x[2], row_n.x[3]);
+#pragma unroll
+            for (int i = 0; i < NIN; ++i) sIn[tid * NIN + i] = row_n.in[i];
+            uint8_t* aug = smem + OFF_ACT + 2 * PANEL;
+            const uint32_t o0 = chunk_off(tid, 0), o1 = chunk_off(tid, 2);
+            *reinterpret_cast<float4*>(aug + o0) = make_float4(xh[0], xh[1], xh[2], xh[3]);
+            *reinterpret_cast<float4*>(aug + o0 + 16) = make_float4(xh[4], xh[5], xh[6], xh[7]);
+            *reinterpret_cast<float4*>(aug + o1) = make_float4(xl[0], xl[1], xl[2], xl[3]);
+            *reinterpret_cast<float4*>(aug + o1 + 16) = make_float4(xl[4], xl[5], xl[6], xl[7]);
+            src_n = src_nn;
+            row_n = load_row<O, A>(a, src_n);
+            src_nn = tile_src(a, tile + 2 * (int64_t)gridDim.x, ntiles, tid);
+        }
+        __syncthreads();
+        // ---- L1: h1 = tanh(W1 x + b1); a quarter-warp writes the 8 chunks of one row (conflict-free)
+        {
+            const int pn = w & 1, rbk = w >> 1, j = l & 7, rs = l >> 3, f0 = 32 * pn + 4 * j;
+            float w1[4][O], bb[4];
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+                bb[q] = sB1[f0 + q];
+#pragma unroll
+                for (int o = 0; o < O; ++o) w1[q][o] = sW1[(f0 + q) * O + o];
+            }
+            uint8_t* hp = smem + OFF_ACT + pn * PANEL;
+            uint8_t* lp = smem + OFF_ACT + (3 + pn) * PANEL;
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+                const int r = 16 * rbk + rs + 4 * i;
+                const float4 xv = *reinterpret_cast<const float4*>(sX + r * 4);
+                const float x[4] = {xv.x, xv.y, xv.z, xv.w};
+                float h[4];
+#pragma unroll
+                for (int q = 0; q < 4; ++q) {
+                    float z = bb[q];
+#pragma unroll
+                    for (int o = 0; o < O; ++o) z = fmaf(w1[q][o], x[o], z);
+                    h[q] = TC_TANH(z);
+                }
+                store_split4(hp, lp, chunk_off(r, j), h);
+            }
+        }
+        fence_async_smem();
+        __syncthreads();
+        if (tid == 0) {
+            tc_after_sync();
+            issue_gemm1(sb, tmem);
+            umma_commit(bar1);
+        }
+        mbar_wait(bar1, par);
+        tc_after_sync();
+        // ---- EPI1: h2, mu, loss, dz2
+        float h2[16];  // [4i + 2*row + e]
+        {
+            float z[16];
+            tmem_ld_frag(tfrag, z);
+            float mpa[A], mpb[A];
+#pragma unroll
+            for (int q = 0; q < A; ++q) { mpa[q] = 0.0f; mpb[q] = 0.0f; }
+#pragma unroll
+            for (int i = 0; i < 4; ++i)
+#pragma unroll
+                for (int e = 0; e < 2; ++e) {
+                    const float ha = TC_TANH(z[4 * i + e] + b2c[2 * i + e]);
+                    const float hb = TC_TANH(z[4 * i + 2 + e] + b2c[2 * i + e]);
+                    h2[4 * i + e] = ha;
+                    h2[4 * i + 2 + e] = hb;
+#pragma unroll
+                    for (int q = 0; q < A; ++q) {
+                        mpa[q] = fmaf(w3c[q][2 * i + e], ha, mpa[q]);
+                        mpb[q] = fmaf(w3c[q][2 * i + e], hb, mpb[q]);
+                    }
+                }
+#pragma unroll
+            for (int q = 0; q < A; ++q) {
+                mpa[q] += __shfl_xor_sync(0xffffffffu, mpa[q], 1);
+                mpb[q] += __shfl_xor_sync(0xffffffffu, mpb[q], 1);
+                mpa[q] += __shfl_xor_sync(0xffffffffu, mpa[q], 2);
+                mpb[q] += __shfl_xor_sync(0xffffffffu, mpb[q], 2);
+                if (p == 0) {
+                    sMu[(hf * A + q) * R + ra] = mpa[q];
+                    sMu[(hf * A + q) * R + rb] = mpb[q];
+                }
+            }
+        }
+        __syncthreads();
+        {
+            float dmu[2][A];
+#pragma unroll
+            for (int s = 0; s < 2; ++s) {
+                const int r = s ? rb : ra;
+                float mu[A];
+#pragma unroll
+                for (int q = 0; q < A; ++q) {
+                    mu[q] = sB3[q] + sMu[q * R + r] + sMu[(A + q) * R + r];
+                    dmu[s][q] = 0.0f;
+                }
+                if (sSrc[r] >= 0) {
+                    MlpRowIn<A> in;
+#pragma unroll
+                    for (int q = 0; q < A; ++q) { in.act[q] = sIn[r * NIN + q]; in.old_mean[q] = 0.0f; }
+                    in.adv = sIn[r * NIN + A]; in.old_logp = sIn[r * NIN + A + 1]; in.ret = sIn[r * NIN + A + 2];
+                    mlp_row_loss<A>(a, in, mu, dist, dmu[s], racc);
+                }
+#pragma unroll
+                for (int q = 0; q < A; ++q) gB3[q] += dmu[s][q];
+            }
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+                float dz[4];  // [2*row + e]
+#pragma unroll
+                for (int s = 0; s < 2; ++s)
+#pragma unroll
+                    for (int e = 0; e < 2; ++e) {
+                        const float h = h2[4 * i + 2 * s + e];
+                        float dh = 0.0f;
+#pragma unroll
+                        for (int q = 0; q < A; ++q) {
+                            dh = fmaf(w3c[q][2 * i + e], dmu[s][q], dh);
+                            gW3[q][2 * i + e] = fmaf(dmu[s][q], h, gW3[q][2 * i + e]);
+                        }
+                        dz[2 * s + e] = dh * (1.0f - h * h);
+                    }
+                store_split2(dz_hi, dz_lo, pair_off(ra, i, p), dz[0], dz[1]);
+                store_split2(dz_hi, dz_lo, pair_off(rb, i, p), dz[2], dz[3]);
+            }
+        }
+        fence_async_smem();
+        tc_before_sync();
+        __syncthreads();
+        if (tid == 0) {
+            tc_after_sync();
+            issue_gemm2(sb, tmem);
+            umma_commit(bar2);
+            issue_gemm3(sb, tmem, it == 0, nks);
+            umma_commit(bar3);
+        }
+        // ---- EPI2: dz1 = dh1 (1 - h1^2)
+        mbar_wait(bar2, par);
+        tc_after_sync();
+        {
+            float d[16];
+            tmem_ld_frag(tfrag, d);
+#pragma unroll
+            for (int i = 0; i < 4; ++i)
+#pragma unroll
+                for (int s = 0; s < 2; ++s) {
+                    const uint32_t off = pair_off(s ? rb : ra, i, p);
+                    const float2 hh = *reinterpret_cast<const float2*>(act_hi + off);
+                    const float2 hl = *reinterpret_cast<const float2*>(act_lo + off);
+                    const float h0 = hh.x + hl.x, h1 = hh.y + hl.y;
+                    d[4 * i + 2 * s] *= (1.0f - h0 * h0);
+                    d[4 * i + 2 * s + 1] *= (1.0f - h1 * h1);
+                }
+            mbar_wait(bar3, par);  // GEMM3 still reads dz2 from the DZ panels
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+                store_split2(dz_hi, dz_lo, pair_off(ra, i, p), d[4 * i], d[4 * i + 1]);
+                store_split2(dz_hi, dz_lo, pair_off(rb, i, p), d[4 * i + 2], d[4 * i + 3]);
+            }
+        }
+        fence_async_smem();
+        tc_before_sync();
+        __syncthreads();
+        if (tid == 0) {
+            tc_after_sync();
+            issue_gemm4(sb, tmem, it == 0, nks);
+            umma_commit(bar4);
+        }
+    }
+    mbar_wait(bar4, (it - 1) & 1);
+    tc_after_sync();
+
+    // ---- write this CTA's partial: [P gradients | MLP_NSTATS statistics]
+    float* out = a.partial + (int64_t)blockIdx.x * (P + MLP_NSTATS);
+    float* scr = reinterpret_cast<float*>(smem + OFF_ACT);
+    constexpr int SW = 81;  // scratch row stride (odd: conflict-free)
+    const uint32_t tlane = tmem + ((uint32_t)(32 * q4) << 16);
+    // G/F lanes 64..127 hold the lo-split halves: park them in smem, lanes 0..63 add, then
+    // every thread stores coalesced
+    if (tid >= 64 && tid < 128) {
+#pragma unroll
+        for (int gq = 0; gq < 5; ++gq) {
+            float v[16];
+            tmem_ld16(tlane + TM_G + 16 * gq, v);
+#pragma unroll
+            for (int i = 0; i < 16; ++i) scr[(tid - 64) * SW + 16 * gq + i] = v[i];
+        }
+    }
+    __syncthreads();
+    if (tid < 64) {
+#pragma unroll
+        for (int gq = 0; gq < 5; ++gq) {
+            float v[16];
+            tmem_ld16(tlane + TM_G + 16 * gq, v);
+#pragma unroll
+            for (int i = 0; i < 16; ++i) scr[tid * SW + 16 * gq + i] += v[i];
+        }
+    }
+    __syncthreads();
+    for (int e = tid; e < H * H; e += NT) out[L.off_w2() + e] = scr[(e >> 6) * SW + (e & 63)];
+    if (tid < H) {
+        out[L.off_b2() + tid] = scr[tid * SW + 64];  // G[:, 64]  (ones column)
+        out[L.off_b1() + tid] = scr[tid * SW + 72];  // F[:, 0]
+    }
+    for (int e = tid; e < H * O; e += NT) out[L.off_w1() + e] = scr[(e / O) * SW + 73 + (e % O)];
+    __syncthreads();
+    // dW3: sum the register accumulators over the 8 row groups of the warp, then over the 4 row quadrants
+    {
+#pragma unroll
+        for (int q = 0; q < A; ++q)
+#pragma unroll
+            for (int c = 0; c < 8; ++c) {
+                float v = gW3[q][c];
+                v += __shfl_xor_sync(0xffffffffu, v, 4);
+                v += __shfl_xor_sync(0xffffffffu, v, 8);
+                v += __shfl_xor_sync(0xffffffffu, v, 16);
+                if (g == 0) scr[(q4 * A + q) * H + c0 + 8 * (c >> 1) + 2 * p + (c & 1)] = v;
+            }
+        __syncthreads();
+        for (int col = tid; col < A * H; col += NT)
+            out[L.off_w3() + col] = (scr[col] + scr[A * H + col]) + (scr[2 * A * H + col] + scr[3 * A * H + col]);
+        __syncthreads();
+    }
+    // row-owned scalars: every row's loss was computed by 8 threads; count one of them
+    {
+        constexpr int NS = A + 1 + 5;
+        float vals[NS];
+        const float keep = (hf == 0 && p == 0) ? 1.0f : 0.0f;
+#pragma unroll
+        for (int q = 0; q < A; ++q) vals[q] = gB3[q] * keep;
+        vals[A] = racc.gLs * keep; vals[A + 1] = racc.st_loss * keep; vals[A + 2] = racc.st_kl * keep;
+        vals[A + 3] = racc.st_ent * keep; vals[A + 4] = racc.st_clip * keep; vals[A + 5] = racc.st_rows * keep;
+#pragma unroll
+        for (int s = 0; s < NS; ++s) {
+            float v = vals[s];
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) v += __shfl_down_sync(0xffffffffu, v, o);
+            if (l == 0) scr[s * 8 + w] = v;
+        }
+        __syncthreads();
+        if (tid < NS) {
+            const float sum = (scr[tid * 8] + scr[tid * 8 + 1]) + (scr[tid * 8 + 2] + scr[tid * 8 + 3]);
+            if (tid < A) out[L.off_b3() + tid] = sum;
+            else if (tid == A) out[L.off_logstd()] = sum;
+            else out[P + (tid - A - 1)] = sum;
+        }
+        if (tid >= NS && tid < NS + (MLP_NSTATS - 5)) out[P + 5 + (tid - NS)] = 0.0f;
+    }
+    tc_before_sync();
+    __syncthreads();
+    if (w == 1) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, 256;" ::"r"(tmem) : "memory");
+}
+}  // namespace tc

@@ -45,6 +45,123 @@ struct MlpArgs {
     unsigned long long* step_counter;  // Adam step, ticked once per backward launch (or NULL)
 };
 
+
+// ---- per-row loss and d loss / d mean, shared by the CUDA-core and the tensor-core kernels
+struct MlpDist {  // the (state-independent) scale of the Gaussian head, gaussian_mlp_module.py:171-176
+    float stdv, var, log_scale;
+    bool ls_pass;  // clamp backward mask
+};
+struct MlpRowAcc {  // row-owned sums: d loss / d log_std and the logging statistics
+    float gLs, st_loss, st_kl, st_ent, st_clip, st_rows;
+};
+
+__device__ __forceinline__ MlpDist mlp_dist(const MlpArgs& a, float raw_ls) {
+    MlpDist d;
+    const float log_std = fminf(fmaxf(raw_ls, a.min_log_std), a.max_log_std);
+    d.ls_pass = (raw_ls >= a.min_log_std) && (raw_ls <= a.max_log_std);
+    d.stdv = expf(log_std);
+    d.var = d.stdv * d.stdv;
+    d.log_scale = logf(d.stdv);
+    return d;
+}
+
+// per-row inputs of the loss (gathered at the minibatch row id)
+template <int A>
+struct MlpRowIn {
+    float act[A], old_mean[A], adv, old_logp, ret;
+};
+template <int A>
+__device__ __forceinline__ MlpRowIn<A> mlp_row_in(const MlpArgs& a, int64_t src) {
+    MlpRowIn<A> in;
+    in.adv = 0.0f; in.old_logp = 0.0f; in.ret = 0.0f;
+#pragma unroll
+    for (int q = 0; q < A; ++q) { in.act[q] = 0.0f; in.old_mean[q] = 0.0f; }
+    if (a.loss_kind == LOSS_VF) {
+        in.ret = a.ret[src];
+    } else if (a.loss_kind != LOSS_NONE) {
+#pragma unroll
+        for (int q = 0; q < A; ++q) in.act[q] = a.act[src * A + q];
+        in.adv = a.adv[src];
+        if (a.loss_kind == LOSS_PPO) in.old_logp = a.old_logp[src];
+        if (a.old_mean) {
+#pragma unroll
+            for (int q = 0; q < A; ++q) in.old_mean[q] = a.old_mean[src * A + q];
+        }
+    }
+    return in;
+}
+
+// loss of one valid row given the network output mu: writes dmu (x 1/mb later), accumulates acc
+template <int A>
+__device__ __forceinline__ void mlp_row_loss(const MlpArgs& a, const MlpRowIn<A>& in, const float (&mu)[A],
+                                             const MlpDist& ds, float (&dmu)[A], MlpRowAcc& acc) {
+    const float var = ds.var, stdv = ds.stdv, log_scale = ds.log_scale;
+    const bool ls_pass = ds.ls_pass;
+    acc.st_rows += 1.0f;
+    // entropy of Independent(Normal): sum_a 0.5 + 0.5 log(2 pi) + log(std)
+    float ent = (float)A * (1.4189385332046727f + log_scale);
+    float dent_dls = (float)A;  // d entropy / d log_std
+    if (a.flags & FLAG_SOFTPLUS_ENT) {  // F.softplus(entropy), vpg.py:429-430
+        const float sp = (ent > 20.0f) ? ent : log1pf(expf(ent));
+        dent_dls *= (ent > 20.0f) ? 1.0f : 1.0f / (1.0f + expf(-ent));
+        ent = sp;
+    }
+    acc.st_ent += ent;
+    if (a.loss_kind == LOSS_NONE) {
+        // forward only (baselines / means)
+    } else if (a.loss_kind == LOSS_VF) {
+        // -log N(ret; mu, std): gaussian_mlp_value_function.py:81-97
+        const float d = in.ret - mu[0];
+        acc.st_loss += (d * d) / (2.0f * var) + log_scale + 0.9189385332046727f;
+        dmu[0] = -d / var;                               // d loss / d mu (x 1/mb later)
+        if (ls_pass) acc.gLs += 1.0f - (d * d) / var;    // d loss / d log_std
+    } else {
+        float ll = 0.0f, dsq = 0.0f, dact[A];
+#pragma unroll
+        for (int q = 0; q < A; ++q) {
+            const float av = in.act[q];
+            ll += normal_logp_term(av, mu[q], var, log_scale);
+            dact[q] = av - mu[q];
+            dsq += dact[q] * dact[q];
+        }
+        const float adv = in.adv;
+        float obj, dobj_dll;
+        if (a.loss_kind == LOSS_PPO) {  // ppo.py:113-132
+            const float ratio = expf(ll - in.old_logp);
+            const float lo = 1.0f - a.clip, hi = 1.0f + a.clip;
+            const float rc = fminf(fmaxf(ratio, lo), hi);
+            const float surr = ratio * adv, surr_c = rc * adv;
+            obj = fminf(surr, surr_c);
+            const bool inside = (ratio >= lo) && (ratio <= hi);
+            // torch.min ties split the gradient, clamp passes it inside [lo,hi]
+            const bool pass = inside || (surr < surr_c);
+            dobj_dll = pass ? ratio * adv : 0.0f;
+            if (!inside) acc.st_clip += 1.0f;
+        } else {  // vpg.py:452-455
+            obj = ll * adv;
+            dobj_dll = adv;
+        }
+        float dobj_dls = 0.0f;
+        if (a.flags & FLAG_ENT_REG) {  // vpg.py:341-343
+            obj += a.ent_coeff * ent;
+            if (!(a.flags & FLAG_STOP_ENT_GRAD)) dobj_dls = a.ent_coeff * dent_dls;
+        }
+        acc.st_loss -= obj;
+#pragma unroll
+        for (int q = 0; q < A; ++q) dmu[q] = -dobj_dll * dact[q] / var;
+        if (ls_pass) acc.gLs -= dobj_dll * (dsq / var - (float)A) + dobj_dls;
+        if (a.old_mean) {  // torch kl_normal_normal(old, new), vpg.py:381-406
+            const float so = expf(a.old_log_std ? __ldg(a.old_log_std) : 0.0f);
+            const float vr = (so / stdv) * (so / stdv);
+#pragma unroll
+            for (int q = 0; q < A; ++q) {
+                const float t1 = (in.old_mean[q] - mu[q]) / stdv;
+                acc.st_kl += 0.5f * (vr + t1 * t1 - 1.0f - logf(vr));
+            }
+        }
+    }
+}
+
 template <int H>
 struct MlpSmem {
     static constexpr int TXN = H / 4, TYN = MLP_NT / TXN, RPT = MLP_R / TYN, KPT = H / TYN;
@@ -94,16 +211,14 @@ __global__ void __launch_bounds__(MLP_NT, 2) mlp_train_kernel(const MlpArgs a) {
     }
     for (int i = tid; i < A * H; i += MLP_NT) sW3[i] = a.params[L.off_w3() + i];
     if (tid < A) sB3[tid] = a.params[L.off_b3() + tid];
-    const float raw_ls = a.params[L.off_logstd()];
-    const float log_std = fminf(fmaxf(raw_ls, a.min_log_std), a.max_log_std);
-    const bool ls_pass = (raw_ls >= a.min_log_std) && (raw_ls <= a.max_log_std);  // clamp backward mask
-    const float stdv = expf(log_std), var = stdv * stdv, log_scale = logf(stdv);
+    const MlpDist dist = mlp_dist(a, a.params[L.off_logstd()]);
     if (BWD && a.step_counter && blockIdx.x == 0 && tid == 0) *a.step_counter += 1ull;
     __syncthreads();
 
     // ---- persistent gradient accumulators
     float gW2[4][KPT], gW3[A][4], gB2[4], gW1[4][O], gB1[4];
-    float gB3[A], gLs = 0.0f, st_loss = 0.0f, st_kl = 0.0f, st_ent = 0.0f, st_clip = 0.0f, st_rows = 0.0f;
+    float gB3[A];
+    MlpRowAcc racc{};
 #pragma unroll
     for (int i = 0; i < 4; ++i) {
 #pragma unroll
@@ -211,69 +326,7 @@ __global__ void __launch_bounds__(MLP_NT, 2) mlp_train_kernel(const MlpArgs a) {
 #pragma unroll
                     for (int q = 0; q < A; ++q) a.mean_out[(m0 + tid) * A + q] = mu[q];
                 }
-                st_rows += 1.0f;
-                // entropy of Independent(Normal): sum_a 0.5 + 0.5 log(2 pi) + log(std)
-                float ent = (float)A * (1.4189385332046727f + log_scale);
-                float dent_dls = (float)A;  // d entropy / d log_std
-                if (a.flags & FLAG_SOFTPLUS_ENT) {  // F.softplus(entropy), vpg.py:429-430
-                    const float sp = (ent > 20.0f) ? ent : log1pf(expf(ent));
-                    dent_dls *= (ent > 20.0f) ? 1.0f : 1.0f / (1.0f + expf(-ent));
-                    ent = sp;
-                }
-                st_ent += ent;
-                if (a.loss_kind == LOSS_NONE) {
-                    // forward only (baselines / means)
-                } else if (a.loss_kind == LOSS_VF) {
-                    // -log N(ret; mu, std): gaussian_mlp_value_function.py:81-97
-                    const float d = a.ret[src] - mu[0];
-                    st_loss += (d * d) / (2.0f * var) + log_scale + 0.9189385332046727f;
-                    dmu[0] = -d / var;                           // d loss / d mu (x 1/mb later)
-                    if (ls_pass) gLs += 1.0f - (d * d) / var;    // d loss / d log_std
-                } else {
-                    float ll = 0.0f, dsq = 0.0f, dact[A];
-#pragma unroll
-                    for (int q = 0; q < A; ++q) {
-                        const float av = a.act[src * A + q];
-                        ll += normal_logp_term(av, mu[q], var, log_scale);
-                        dact[q] = av - mu[q];
-                        dsq += dact[q] * dact[q];
-                    }
-                    const float adv = a.adv[src];
-                    float obj, dobj_dll;
-                    if (a.loss_kind == LOSS_PPO) {  // ppo.py:113-132
-                        const float ratio = expf(ll - a.old_logp[src]);
-                        const float lo = 1.0f - a.clip, hi = 1.0f + a.clip;
-                        const float rc = fminf(fmaxf(ratio, lo), hi);
-                        const float surr = ratio * adv, surr_c = rc * adv;
-                        obj = fminf(surr, surr_c);
-                        const bool inside = (ratio >= lo) && (ratio <= hi);
-                        // torch.min ties split the gradient, clamp passes it inside [lo,hi]
-                        const bool pass = inside || (surr < surr_c);
-                        dobj_dll = pass ? ratio * adv : 0.0f;
-                        if (!inside) st_clip += 1.0f;
-                    } else {  // vpg.py:452-455
-                        obj = ll * adv;
-                        dobj_dll = adv;
-                    }
-                    float dobj_dls = 0.0f;
-                    if (a.flags & FLAG_ENT_REG) {  // vpg.py:341-343
-                        obj += a.ent_coeff * ent;
-                        if (!(a.flags & FLAG_STOP_ENT_GRAD)) dobj_dls = a.ent_coeff * dent_dls;
-                    }
-                    st_loss -= obj;
-#pragma unroll
-                    for (int q = 0; q < A; ++q) dmu[q] = -dobj_dll * dact[q] / var;
-                    if (ls_pass) gLs -= dobj_dll * (dsq / var - (float)A) + dobj_dls;
-                    if (a.old_mean) {  // torch kl_normal_normal(old, new), vpg.py:381-406
-                        const float so = expf(a.old_log_std ? __ldg(a.old_log_std) : 0.0f);
-                        const float vr = (so / stdv) * (so / stdv);
-#pragma unroll
-                        for (int q = 0; q < A; ++q) {
-                            const float t1 = (a.old_mean[src * A + q] - mu[q]) / stdv;
-                            st_kl += 0.5f * (vr + t1 * t1 - 1.0f - logf(vr));
-                        }
-                    }
-                }
+                mlp_row_loss<A>(a, mlp_row_in<A>(a, src), mu, dist, dmu, racc);
             }
             if (BWD) {
 #pragma unroll
@@ -438,8 +491,8 @@ __global__ void __launch_bounds__(MLP_NT, 2) mlp_train_kernel(const MlpArgs a) {
         float vals[NS];
 #pragma unroll
         for (int q = 0; q < A; ++q) vals[q] = gB3[q];
-        vals[A] = gLs; vals[A + 1] = st_loss; vals[A + 2] = st_kl; vals[A + 3] = st_ent;
-        vals[A + 4] = st_clip; vals[A + 5] = st_rows;
+        vals[A] = racc.gLs; vals[A + 1] = racc.st_loss; vals[A + 2] = racc.st_kl; vals[A + 3] = racc.st_ent;
+        vals[A + 4] = racc.st_clip; vals[A + 5] = racc.st_rows;
 #pragma unroll
         for (int s = 0; s < NS; ++s) {
             float v = vals[s];

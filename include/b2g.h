@@ -255,6 +255,12 @@ int b2g_policy_sample(const float* mean, int act_dim, float log_std, uint64_t se
 #define B2G_MLP_NSTATS 8
 
 int b2g_mlp_num_partials(int obs_dim, int hidden, int out_dim, int backward, int64_t rows);
+/* Arithmetic path of b2g_mlp_minibatch_grad: 0 = auto (hidden 64: tcgen05 kind::tf32 with a
+ * 3xTF32 hi/lo split, fp32 accumulation in tensor memory; otherwise CUDA-core fp32),
+ * 1 = CUDA-core fp32 for every shape, 2 = same as 0.  Also selectable with the environment
+ * variable B2G_MLP_PATH=ffma.  Both paths meet the 1e-5 parity bar of the same reference code. */
+int b2g_set_mlp_path(int path);
+int b2g_get_mlp_path(void);
 int64_t b2g_mlp_ws_floats(int obs_dim, int hidden, int out_dim);
 
 int b2g_mlp_minibatch_grad(int obs_dim, int hidden, int out_dim, const float* params,
