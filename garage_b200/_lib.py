@@ -47,6 +47,7 @@ SIGNATURES = {
     'b2g_mlp_num_partials': (c_int, [c_int, c_int, c_int, c_int, c_int64]),
     'b2g_set_mlp_path': (c_int, [c_int]),
     'b2g_get_mlp_path': (c_int, []),
+    'b2g_mlp_debug_timing': (c_int, [P]),
     'b2g_mlp_ws_floats': (c_int64, [c_int, c_int, c_int]),
     'b2g_mlp_minibatch_grad': (c_int, [c_int, c_int, c_int, P, P, c_int64, c_int64, P, P, P, P, P,
                                        c_int, c_int, c_float, c_float, c_float, c_float, P, P, P]),

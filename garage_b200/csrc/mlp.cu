@@ -53,6 +53,10 @@ extern "C" int b2g_set_mlp_path(int path) {
 }
 extern "C" int b2g_get_mlp_path(void) { return mlp_path(); }
 
+// debug hook (tools/profile_mlp.py --timing): device buffer [grid][32] of clock64 stamps
+static long long* g_mlp_timing = nullptr;
+extern "C" int b2g_mlp_debug_timing(long long* buf) { g_mlp_timing = buf; return B2G_OK; }
+
 template <int H, int O, int A>
 constexpr bool mlp_has_tc() { return H == 64; }
 
@@ -134,7 +138,7 @@ extern "C" int b2g_mlp_minibatch_grad(int obs_dim, int hidden, int out_dim, cons
     a.adv = adv; a.old_logp = old_logp; a.ret = ret; a.old_mean = nullptr; a.old_log_std = nullptr;
     a.loss_kind = loss_kind; a.flags = flags; a.clip = clip; a.ent_coeff = ent_coeff;
     a.min_log_std = min_log_std; a.max_log_std = max_log_std; a.partial = ws_partial;
-    a.mean_out = nullptr; a.step_counter = step_counter;
+    a.mean_out = nullptr; a.step_counter = step_counter; a.timing = g_mlp_timing;
     return dispatch_mlp<true>(obs_dim, hidden, out_dim, a, (cudaStream_t)stream);
 }
 

@@ -26,10 +26,11 @@
 //   GEMM1  D[r][c]  = sum_k h1[r][k] W2[c][k]        M64 N64    A=ACT (K-major)  B=W (K-major)
 //   EPI1   h2 = tanh(D + b2); mu = W3 h2 + b3; loss; dz2        -> DZ panels hi0 hi1 lo0 lo1
 //   GEMM2  D[r][k]  = sum_c dz2[r][c] W2[c][k]       M64 N64    A=DZ (K-major)   B=W (MN-major)
-//   GEMM3  G[m][n] += sum_r dz2{hi|lo}[r][m] [h1|1|x][r][n]   M128(hi;lo stacked) N72/64, MN/MN
+//   GEMM3  G[m][n] += sum_r dz2{hi|lo}[r][m] [h1hi|1 x|h1lo][r][n]  M128(hi;lo stacked) N160, MN/MN
 //   EPI2   dz1 = D (1 - h1^2)                                   -> DZ panels (after GEMM3 drained)
-//   GEMM4  F[m][n] += sum_r dz1{hi|lo}[r][m] [1|x][r][n]       M128 N8, MN/MN
-// dW2 = G[0:64, 0:64] + G[64:128, 0:64], db2 = G[:, 64], db1 = F[:, 0], dW1 = F[:, 1:1+O];
+//   GEMM4  F[m][n] += sum_r dz1{hi|lo}[r][m] [1 xhi|0 xlo][r][n]  M128 N16, MN/MN
+// dW2 = G[:, 0:64] + G[:, 96:160] (lanes m and m+64 added), db2 = G[:, 64], db1 = F[:, 0],
+// dW1 = F[:, 1:1+O] + F[:, 9:9+O];
 // dW3 accumulates in registers, db3 / dlog_std / statistics are row sums as in mlp_train.cuh.
 // The M=64 accumulator D lives in TMEM lanes (m%16) + 32*(m/16); the epilogues read it with
 // tcgen05.ld.16x256b (thread t of warp q: rows 16q + t/4 and +8, column pairs 8i + 2(t%4)),
@@ -44,7 +45,7 @@ constexpr uint32_t OFF_ACT = 0;                      // 5 panels: hi0 hi1 aug lo
 constexpr uint32_t OFF_DZ = OFF_ACT + 5 * PANEL;     // 4 panels: hi0 hi1 lo0 lo1
 constexpr uint32_t OFF_W = OFF_DZ + 4 * PANEL;       // 4 weight panels: hi0 hi1 lo0 lo1
 constexpr uint32_t OFF_SMALL = OFF_W + 4 * WPANEL;   // 106,496
-constexpr uint32_t TM_D = 0, TM_G = 64, TM_F = 136;
+constexpr uint32_t TM_D = 0, TM_G = 64, TM_F = 224;  // D 64 | G 160 (h1hi 64, aug 32, h1lo 64) | F 16 columns
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
 
@@ -71,6 +72,13 @@ __device__ __forceinline__ void umma_commit(uint32_t bar) {
 __device__ __forceinline__ void fence_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
 __device__ __forceinline__ void tc_before_sync() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void tc_after_sync() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+
+// one lane of a converged warp
+__device__ __forceinline__ bool elect_one() {
+    uint32_t pred;
+    asm volatile("{\n\t.reg .pred p;\n\telect.sync _|p, 0xffffffff;\n\tselp.u32 %0, 1, 0, p;\n\t}\n" : "=r"(pred));
+    return pred != 0;
+}
 
 // bounded spin: a lost MMA completion must surface as an error, not as a hung GPU
 __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
@@ -182,30 +190,25 @@ __device__ __forceinline__ void issue_gemm2(uint32_t sb, uint32_t tmem) {
                       umma_desc(sb + bo + ks * 1024, WPANEL, 512), ID, (pass | ks) != 0);
     }
 }
-// nks = ceil(valid rows / 8): rows past the minibatch contribute nothing and are skipped
+// nks = ceil(valid rows / 8): rows past the minibatch contribute nothing and are skipped.
+// One MMA per K step covers all five ACT panels (N = 160: h1 hi | aug | h1 lo), so the stacked
+// dz2 operand is fetched from shared memory once.
 __device__ __forceinline__ void issue_gemm3(uint32_t sb, uint32_t tmem, bool first, int nks) {
-    constexpr uint32_t ID72 = umma_idesc(128, 72, 1, 1), ID64 = umma_idesc(128, 64, 1, 1);
+    constexpr uint32_t ID = umma_idesc(128, 160, 1, 1);
 #pragma unroll
     for (int ks = 0; ks < R / 8; ++ks)
         if (ks < nks)
             umma_tf32(tmem + TM_G, umma_desc(sb + OFF_DZ + ks * 1024, PANEL, 512),
-                      umma_desc(sb + OFF_ACT + ks * 1024, PANEL, 512), ID72, !(first && ks == 0));
-#pragma unroll
-    for (int ks = 0; ks < R / 8; ++ks)
-        if (ks < nks)
-            umma_tf32(tmem + TM_G, umma_desc(sb + OFF_DZ + ks * 1024, PANEL, 512),
-                      umma_desc(sb + OFF_ACT + 3 * PANEL + ks * 1024, PANEL, 512), ID64, 1);
+                      umma_desc(sb + OFF_ACT + ks * 1024, PANEL, 512), ID, !(first && ks == 0));
 }
+// N = 16: [1 x_hi 0.. | 0 x_lo 0..] of the aug panel
 __device__ __forceinline__ void issue_gemm4(uint32_t sb, uint32_t tmem, bool first, int nks) {
-    constexpr uint32_t ID8 = umma_idesc(128, 8, 1, 1);
+    constexpr uint32_t ID = umma_idesc(128, 16, 1, 1);
 #pragma unroll
-    for (int pass = 0; pass < 2; ++pass)
-#pragma unroll
-        for (int ks = 0; ks < R / 8; ++ks)
-            if (ks < nks)
-                umma_tf32(tmem + TM_F, umma_desc(sb + OFF_DZ + ks * 1024, PANEL, 512),
-                          umma_desc(sb + OFF_ACT + 2 * PANEL + pass * 32 + ks * 1024, PANEL, 512), ID8,
-                          !(first && pass == 0 && ks == 0));
+    for (int ks = 0; ks < R / 8; ++ks)
+        if (ks < nks)
+            umma_tf32(tmem + TM_F, umma_desc(sb + OFF_DZ + ks * 1024, PANEL, 512),
+                      umma_desc(sb + OFF_ACT + 2 * PANEL + ks * 1024, PANEL, 512), ID, !(first && ks == 0));
 }
 
 template <int O, int A>
@@ -268,8 +271,10 @@ __global__ void __launch_bounds__(NT, 2) mlp_train_tc_kernel(const MlpArgs a) {
     uint32_t* tslot = reinterpret_cast<uint32_t*>(sm + S::TSLOT);
     const uint32_t sb = smem_u32(smem);
     const uint32_t bar1 = smem_u32(sm + S::BARS), bar2 = bar1 + 8, bar3 = bar1 + 16, bar4 = bar1 + 24;
-    const int tid = threadIdx.x, w = tid >> 5, l = tid & 31;
+    const int tid = threadIdx.x, w = __shfl_sync(0xffffffffu, tid >> 5, 0), l = tid & 31;  // w: provably warp-uniform
     const int64_t ntiles = (a.mb + R - 1) / R;
+#define TC_STAMP(i) do { if (a.timing && tid == 0 && (i) < 32) a.timing[blockIdx.x * 32 + (i)] = clock64(); } while (0)
+    TC_STAMP(0);
 
     // ---- gather pipeline (threads 0..R-1 own one row): row ids run two tiles ahead of the
     // tile being computed, row data one tile ahead, so no stage waits on a dependent load
@@ -306,6 +311,8 @@ __global__ void __launch_bounds__(NT, 2) mlp_train_tc_kernel(const MlpArgs a) {
             store_split4(smem + OFF_W, smem + OFF_W + 2 * WPANEL, off, v[i]);
         }
     }
+    for (int i = tid; i < (int)(PANEL / 16); i += NT)  // aug panel: columns 16..31 are never written
+        reinterpret_cast<float4*>(smem + OFF_ACT + 2 * PANEL)[i] = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
     for (int i = tid; i < H * O; i += NT) sW1[i] = a.params[L.off_w1() + i];
     if (tid < H) {
         sB1[tid] = a.params[L.off_b1() + tid];
@@ -319,7 +326,8 @@ __global__ void __launch_bounds__(NT, 2) mlp_train_tc_kernel(const MlpArgs a) {
     tc_before_sync();
     __syncthreads();
     tc_after_sync();
-    const uint32_t tmem = *tslot;
+    const uint32_t tmem = __shfl_sync(0xffffffffu, *tslot, 0);
+    TC_STAMP(1);
 
     // ---- epilogue role: rows ra = 16q + g and rb = ra + 8, feature pairs 32hf + 8i + 2p (+1)
     const int q4 = w & 3, hf = w >> 2, g = l >> 2, p = l & 3;
@@ -355,6 +363,7 @@ __global__ void __launch_bounds__(NT, 2) mlp_train_tc_kernel(const MlpArgs a) {
         const int valid = (int)((a.mb - m0) < R ? (a.mb - m0) : R);
         const int nks = (valid + 7) >> 3;
         if (it > 0) mbar_wait(bar4, par ^ 1);  // every MMA of the previous tile has drained
+        TC_STAMP(2 + 10 * it);
         // ---- publish this tile's rows; aug panel row = [1 x_hi 0.. | 0 x_lo 0..]; prefetch ahead
         if (tid < R) {
             sSrc[tid] = src_n;
@@ -378,6 +387,7 @@ __global__ void __launch_bounds__(NT, 2) mlp_train_tc_kernel(const MlpArgs a) {
             src_nn = tile_src(a, tile + 2 * (int64_t)gridDim.x, ntiles, tid);
         }
         __syncthreads();
+        TC_STAMP(3 + 10 * it);
         // ---- L1: h1 = tanh(W1 x + b1); a quarter-warp writes the 8 chunks of one row (conflict-free)
         {
             const int pn = w & 1, rbk = w >> 1, j = l & 7, rs = l >> 3, f0 = 32 * pn + 4 * j;
@@ -406,15 +416,22 @@ __global__ void __launch_bounds__(NT, 2) mlp_train_tc_kernel(const MlpArgs a) {
                 store_split4(hp, lp, chunk_off(r, j), h);
             }
         }
+        TC_STAMP(4 + 10 * it);
         fence_async_smem();
         __syncthreads();
-        if (tid == 0) {
+        if (it == 0) TC_STAMP(22);
+        if (w == 0) {  // descriptors stay in uniform registers: the whole warp takes the branch
             tc_after_sync();
-            issue_gemm1(sb, tmem);
-            umma_commit(bar1);
+            if (elect_one()) {
+                issue_gemm1(sb, tmem);
+                umma_commit(bar1);
+            }
+            __syncwarp();
         }
+        TC_STAMP(5 + 10 * it);
         mbar_wait(bar1, par);
         tc_after_sync();
+        TC_STAMP(6 + 10 * it);
         // ---- EPI1: h2, mu, loss, dz2
         float h2[16];  // [4i + 2*row + e]
         {
@@ -451,25 +468,30 @@ __global__ void __launch_bounds__(NT, 2) mlp_train_tc_kernel(const MlpArgs a) {
         }
         __syncthreads();
         {
+            // the loss of a row is evaluated by the lanes p and p^2 of its quad (p&1 picks the row),
+            // then handed to the other lanes: half the instructions of evaluating both rows everywhere
             float dmu[2][A];
-#pragma unroll
-            for (int s = 0; s < 2; ++s) {
-                const int r = s ? rb : ra;
-                float mu[A];
+            {
+                const int r = (p & 1) ? rb : ra;
+                float mu[A], dm[A];
 #pragma unroll
                 for (int q = 0; q < A; ++q) {
                     mu[q] = sB3[q] + sMu[q * R + r] + sMu[(A + q) * R + r];
-                    dmu[s][q] = 0.0f;
+                    dm[q] = 0.0f;
                 }
                 if (sSrc[r] >= 0) {
                     MlpRowIn<A> in;
 #pragma unroll
                     for (int q = 0; q < A; ++q) { in.act[q] = sIn[r * NIN + q]; in.old_mean[q] = 0.0f; }
                     in.adv = sIn[r * NIN + A]; in.old_logp = sIn[r * NIN + A + 1]; in.ret = sIn[r * NIN + A + 2];
-                    mlp_row_loss<A>(a, in, mu, dist, dmu[s], racc);
+                    mlp_row_loss<A>(a, in, mu, dist, dm, racc);
                 }
 #pragma unroll
-                for (int q = 0; q < A; ++q) gB3[q] += dmu[s][q];
+                for (int q = 0; q < A; ++q) {
+                    gB3[q] += dm[q];
+                    dmu[0][q] = __shfl_sync(0xffffffffu, dm[q], l & ~3);
+                    dmu[1][q] = __shfl_sync(0xffffffffu, dm[q], (l & ~3) | 1);
+                }
             }
 #pragma unroll
             for (int i = 0; i < 4; ++i) {
@@ -491,19 +513,27 @@ __global__ void __launch_bounds__(NT, 2) mlp_train_tc_kernel(const MlpArgs a) {
                 store_split2(dz_hi, dz_lo, pair_off(rb, i, p), dz[2], dz[3]);
             }
         }
+        TC_STAMP(7 + 10 * it);
         fence_async_smem();
         tc_before_sync();
         __syncthreads();
-        if (tid == 0) {
+        if (it == 0) TC_STAMP(23);
+        if (w == 0) {
             tc_after_sync();
-            issue_gemm2(sb, tmem);
-            umma_commit(bar2);
-            issue_gemm3(sb, tmem, it == 0, nks);
-            umma_commit(bar3);
+            if (elect_one()) {
+                issue_gemm2(sb, tmem);
+                umma_commit(bar2);
+                if (it == 0 && a.timing) a.timing[blockIdx.x * 32 + 24] = clock64();
+                issue_gemm3(sb, tmem, it == 0, nks);
+                umma_commit(bar3);
+            }
+            __syncwarp();
         }
         // ---- EPI2: dz1 = dh1 (1 - h1^2)
+        TC_STAMP(8 + 10 * it);
         mbar_wait(bar2, par);
         tc_after_sync();
+        TC_STAMP(9 + 10 * it);
         {
             float d[16];
             tmem_ld_frag(tfrag, d);
@@ -519,6 +549,7 @@ __global__ void __launch_bounds__(NT, 2) mlp_train_tc_kernel(const MlpArgs a) {
                     d[4 * i + 2 * s + 1] *= (1.0f - h1 * h1);
                 }
             mbar_wait(bar3, par);  // GEMM3 still reads dz2 from the DZ panels
+            TC_STAMP(10 + 10 * it);
 #pragma unroll
             for (int i = 0; i < 4; ++i) {
                 store_split2(dz_hi, dz_lo, pair_off(ra, i, p), d[4 * i], d[4 * i + 1]);
@@ -528,40 +559,66 @@ __global__ void __launch_bounds__(NT, 2) mlp_train_tc_kernel(const MlpArgs a) {
         fence_async_smem();
         tc_before_sync();
         __syncthreads();
-        if (tid == 0) {
+        if (w == 0) {
             tc_after_sync();
-            issue_gemm4(sb, tmem, it == 0, nks);
-            umma_commit(bar4);
+            if (elect_one()) {
+                issue_gemm4(sb, tmem, it == 0, nks);
+                umma_commit(bar4);
+            }
+            __syncwarp();
         }
+        TC_STAMP(11 + 10 * it);
     }
+    TC_STAMP(28);
     mbar_wait(bar4, (it - 1) & 1);
     tc_after_sync();
+    TC_STAMP(29);
 
     // ---- write this CTA's partial: [P gradients | MLP_NSTATS statistics]
     float* out = a.partial + (int64_t)blockIdx.x * (P + MLP_NSTATS);
     float* scr = reinterpret_cast<float*>(smem + OFF_ACT);
     constexpr int SW = 81;  // scratch row stride (odd: conflict-free)
     const uint32_t tlane = tmem + ((uint32_t)(32 * q4) << 16);
-    // G/F lanes 64..127 hold the lo-split halves: park them in smem, lanes 0..63 add, then
-    // every thread stores coalesced
-    if (tid >= 64 && tid < 128) {
+    // every lane folds its own hi/lo column groups; lanes 64..127 (the lo-split rows) park the
+    // result in smem, lanes 0..63 add theirs, then every thread stores coalesced
+    if (tid < 128) {
+        const int m = tid & 63;
+        const bool lo_rows = tid >= 64;
 #pragma unroll
-        for (int gq = 0; gq < 5; ++gq) {
-            float v[16];
+        for (int gq = 0; gq < 4; ++gq) {
+            float v[16], u[16];
             tmem_ld16(tlane + TM_G + 16 * gq, v);
+            tmem_ld16(tlane + TM_G + 96 + 16 * gq, u);
+            if (lo_rows) {
 #pragma unroll
-            for (int i = 0; i < 16; ++i) scr[(tid - 64) * SW + 16 * gq + i] = v[i];
+                for (int i = 0; i < 16; ++i) scr[m * SW + 16 * gq + i] = v[i] + u[i];
+            }
+        }
+        float v[16], f[16];
+        tmem_ld16(tlane + TM_G + 64, v);
+        tmem_ld16(tlane + TM_F, f);
+        if (lo_rows) {
+            scr[m * SW + 64] = v[0];
+#pragma unroll
+            for (int i = 0; i < 8; ++i) scr[m * SW + 72 + i] = f[i] + f[8 + i];
         }
     }
     __syncthreads();
     if (tid < 64) {
 #pragma unroll
-        for (int gq = 0; gq < 5; ++gq) {
-            float v[16];
+        for (int gq = 0; gq < 4; ++gq) {
+            float v[16], u[16];
             tmem_ld16(tlane + TM_G + 16 * gq, v);
+            tmem_ld16(tlane + TM_G + 96 + 16 * gq, u);
 #pragma unroll
-            for (int i = 0; i < 16; ++i) scr[tid * SW + 16 * gq + i] += v[i];
+            for (int i = 0; i < 16; ++i) scr[tid * SW + 16 * gq + i] += v[i] + u[i];
         }
+        float v[16], f[16];
+        tmem_ld16(tlane + TM_G + 64, v);
+        tmem_ld16(tlane + TM_F, f);
+        scr[tid * SW + 64] += v[0];
+#pragma unroll
+        for (int i = 0; i < 8; ++i) scr[tid * SW + 72 + i] += f[i] + f[8 + i];
     }
     __syncthreads();
     for (int e = tid; e < H * H; e += NT) out[L.off_w2() + e] = scr[(e >> 6) * SW + (e & 63)];
@@ -588,11 +645,11 @@ __global__ void __launch_bounds__(NT, 2) mlp_train_tc_kernel(const MlpArgs a) {
             out[L.off_w3() + col] = (scr[col] + scr[A * H + col]) + (scr[2 * A * H + col] + scr[3 * A * H + col]);
         __syncthreads();
     }
-    // row-owned scalars: every row's loss was computed by 8 threads; count one of them
+    // row-owned scalars: every row's loss was computed by 4 threads; count one of them
     {
         constexpr int NS = A + 1 + 5;
         float vals[NS];
-        const float keep = (hf == 0 && p == 0) ? 1.0f : 0.0f;
+        const float keep = (hf == 0 && p < 2) ? 1.0f : 0.0f;
 #pragma unroll
         for (int q = 0; q < A; ++q) vals[q] = gB3[q] * keep;
         vals[A] = racc.gLs * keep; vals[A + 1] = racc.st_loss * keep; vals[A + 2] = racc.st_kl * keep;
@@ -613,6 +670,7 @@ __global__ void __launch_bounds__(NT, 2) mlp_train_tc_kernel(const MlpArgs a) {
         }
         if (tid >= NS && tid < NS + (MLP_NSTATS - 5)) out[P + 5 + (tid - NS)] = 0.0f;
     }
+    TC_STAMP(30);
     tc_before_sync();
     __syncthreads();
     if (w == 1) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, 256;" ::"r"(tmem) : "memory");

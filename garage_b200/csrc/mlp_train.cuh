@@ -43,6 +43,7 @@ struct MlpArgs {
     float* partial;         // [grid][P + MLP_NSTATS]
     float* mean_out;        // [mb,A] or NULL (forward output, minibatch order)
     unsigned long long* step_counter;  // Adam step, ticked once per backward launch (or NULL)
+    long long* timing;      // debug: [grid][32] clock64 stamps of the tensor-core kernel (or NULL)
 };
 
 

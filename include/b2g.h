@@ -261,6 +261,9 @@ int b2g_mlp_num_partials(int obs_dim, int hidden, int out_dim, int backward, int
  * variable B2G_MLP_PATH=ffma.  Both paths meet the 1e-5 parity bar of the same reference code. */
 int b2g_set_mlp_path(int path);
 int b2g_get_mlp_path(void);
+/* Debug only: device buffer [grid][32] of int64 that the tcgen05 kernel fills with clock64()
+ * stamps of its stages (NULL switches it off, the default). */
+int b2g_mlp_debug_timing(long long* buf);
 int64_t b2g_mlp_ws_floats(int obs_dim, int hidden, int out_dim);
 
 int b2g_mlp_minibatch_grad(int obs_dim, int hidden, int out_dim, const float* params,

@@ -16,6 +16,7 @@ def main():
     ap.add_argument('--mb', type=int, default=32768)
     ap.add_argument('--reps', type=int, default=20)
     ap.add_argument('--vf', action='store_true')
+    ap.add_argument('--timing', action='store_true')
     a = ap.parse_args()
     dev = torch.device('cuda:0')
     g = torch.Generator(device=dev).manual_seed(0)
@@ -41,6 +42,32 @@ def main():
         run(r)
     e1.record()
     torch.cuda.synchronize()
+    if a.timing:
+        tb = torch.zeros(296, 32, dtype=torch.int64, device=dev)
+        ops._lib.load().b2g_mlp_debug_timing(tb.data_ptr())
+        run(0)
+        torch.cuda.synchronize()
+        ops._lib.load().b2g_mlp_debug_timing(None)
+        t = tb.cpu().numpy()
+        names = {0: 'start', 1: 'prologue done', 28: 'loop done', 29: 'last MMA drained', 30: 'partials written'}
+        for it in range(2):
+            for k, nm in enumerate(['bar4 waited', 'gather published', 'L1 done', 'GEMM1 issued', 'GEMM1 done',
+                                    'EPI1 done', 'GEMM2/3 issued', 'GEMM2 done', 'GEMM3 done', 'GEMM4 issued']):
+                names[2 + 10 * it + k] = 'tile{} {}'.format(it, nm)
+        names[22] = 'tile0 L1 barrier passed (abs)'; names[23] = 'tile0 EPI1 barrier passed (abs)'; names[24] = 'tile0 GEMM2 issued (abs)'
+        import numpy as np
+        two = t[:, 12] > 0
+        print('CTAs with 2 tiles:', int(two.sum()), 'of', t.shape[0])
+        for sel, label in ((two, '2-tile CTAs'), (~two, '1-tile CTAs')):
+            if not sel.any():
+                continue
+            tt = t[sel]
+            prev = tt[:, 0]
+            print('---', label, '(median cycles since previous stamp / since start)')
+            for i in sorted(names):
+                if (tt[:, i] > 0).all():
+                    print('{:28s} {:8.0f} {:8.0f}'.format(names[i], np.median(tt[:, i] - prev), np.median(tt[:, i] - tt[:, 0])))
+                    prev = tt[:, i]
     print('mlp path', ops._lib.load().b2g_get_mlp_path(), 'us per launch', 1e3 * e0.elapsed_time(e1) / a.reps)
 
 
