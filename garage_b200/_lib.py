@@ -16,6 +16,20 @@ LIB_PATH = os.path.join(_HERE, 'libb2g.so')
 
 P = c_void_p  # every device pointer / stream
 
+
+class TrainNet(ctypes.Structure):
+    """`b2g_train_net` of include/b2g.h (one network of the fused training loop)."""
+    _fields_ = [('obs_dim', c_int), ('hidden', c_int), ('out_dim', c_int),
+                ('params', P), ('adam_m', P), ('adam_v', P), ('step_counter', P),
+                ('lr', c_double), ('beta1', c_double), ('beta2', c_double), ('eps', c_double),
+                ('obs', P), ('act', P), ('adv', P), ('old_logp', P), ('ret', P),
+                ('loss_kind', c_int), ('flags', c_int),
+                ('clip', c_float), ('ent_coeff', c_float), ('min_log_std', c_float), ('max_log_std', c_float),
+                ('n_rows', c_int64), ('minibatch', c_int64),
+                ('epochs', c_int), ('shuffle', c_int),
+                ('shuffle_seed', c_uint64), ('idx', P)]
+
+
 # name -> (restype, argtypes); mirrors include/b2g.h one to one
 SIGNATURES = {
     'b2g_version': (c_int, []),
@@ -57,6 +71,8 @@ SIGNATURES = {
                                c_double, c_double, P]),
     'b2g_adam_step': (c_int, [P, P, c_float, P, P, P, c_double, c_double, c_double, c_double,
                               c_int, P]),
+    'b2g_mlp_train_loop_ws_floats': (c_int64, []),
+    'b2g_mlp_train_loop': (c_int, [POINTER(TrainNet), c_int, P, c_int64, P]),
 }
 
 

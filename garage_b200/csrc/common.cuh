@@ -93,3 +93,40 @@ __host__ __device__ __forceinline__ double b2g_u01d(uint32_t hi, uint32_t lo) {
 
 // Philox stream ids (counter word c2)
 enum : uint32_t { B2G_STREAM_ACTION = 0, B2G_STREAM_RESET = 1, B2G_STREAM_PERM = 2 };
+
+// ------------------------------------------------------------ permutation --
+// Minibatch shuffle without a sort: a keyed balanced Feistel network over the smallest
+// even-width bit domain >= n, cycle-walked back into [0,n).  Counter based (keys =
+// Philox(seed; counter)): the same (seed, counter) gives the same permutation on any number of
+// ranks, and any kernel can evaluate single elements on the fly (b2g_perm_apply).
+__host__ __device__ __forceinline__ uint32_t b2g_mix32(uint32_t x) {
+    x ^= x >> 16; x *= 0x85EBCA6Bu; x ^= x >> 13; x *= 0xC2B2AE35u; x ^= x >> 16;
+    return x;
+}
+__host__ __device__ __forceinline__ void b2g_perm_keys(uint32_t seed_lo, uint32_t seed_hi, uint64_t c, uint32_t* keys) {
+    const Philox4 k0 = b2g_philox(seed_lo, seed_hi, (uint32_t)c, (uint32_t)(c >> 32), B2G_STREAM_PERM, 0);
+    const Philox4 k1 = b2g_philox(seed_lo, seed_hi, (uint32_t)c, (uint32_t)(c >> 32), B2G_STREAM_PERM, 1);
+    keys[0] = k0.x; keys[1] = k0.y; keys[2] = k0.z; keys[3] = k0.w;
+    keys[4] = k1.x; keys[5] = k1.y; keys[6] = k1.z; keys[7] = k1.w;
+}
+__host__ __device__ __forceinline__ int b2g_perm_half_bits(int64_t n) {
+    int bits = 1;
+    while (((int64_t)1 << bits) < n) ++bits;
+    return (bits + 1) / 2 < 1 ? 1 : (bits + 1) / 2;
+}
+__host__ __device__ __forceinline__ uint64_t b2g_perm_apply(const uint32_t* keys, int half_bits, uint64_t n, uint64_t i) {
+    const uint32_t mask = (1u << half_bits) - 1u;
+    uint64_t x = i;
+    do {
+        uint32_t L = (uint32_t)(x >> half_bits) & mask, R = (uint32_t)x & mask;
+#pragma unroll
+        for (int r = 0; r < 8; ++r) {
+            const uint32_t f = b2g_mix32(R ^ keys[r]) & mask;
+            const uint32_t nl = R;
+            R = L ^ f;
+            L = nl;
+        }
+        x = ((uint64_t)L << half_bits) | R;
+    } while (x >= n);
+    return x;
+}

@@ -166,40 +166,18 @@ extern "C" int b2g_normalize_adv(const float* x, const double* stats3, int cente
 }
 
 // ------------------------------------------------------------ permutation --
-// Minibatch shuffle without a sort: a keyed balanced Feistel network over the
-// smallest even-width bit domain >= n, cycle-walked back into [0,n).  Counter
-// based (key = Philox(seed; counter)), so the same (seed, counter) always gives
-// the same permutation, on any number of ranks.  Stands in for
-// np.random.shuffle(self._ids) of np/optimizers/minibatch_dataset.py:35 in
-// throughput mode; parity mode feeds the reference's own index lists instead.
-__device__ __forceinline__ uint32_t mix32(uint32_t x) {
-    x ^= x >> 16; x *= 0x85EBCA6Bu; x ^= x >> 13; x *= 0xC2B2AE35u; x ^= x >> 16;
-    return x;
-}
-
+// Stands in for np.random.shuffle(self._ids) of np/optimizers/minibatch_dataset.py:35 in
+// throughput mode (parity mode feeds the reference's own index lists instead); the Feistel
+// network itself lives in common.cuh (b2g_perm_apply).
 __global__ void __launch_bounds__(256)
 permutation_kernel(uint32_t seed_lo, uint32_t seed_hi, const unsigned long long* __restrict__ counter_dev,
                    uint64_t counter, int64_t n, int half_bits, int32_t* __restrict__ out) {
     const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
     const uint64_t c = counter + (counter_dev ? (uint64_t)*counter_dev : 0ull);
-    const Philox4 k0 = b2g_philox(seed_lo, seed_hi, (uint32_t)c, (uint32_t)(c >> 32), B2G_STREAM_PERM, 0);
-    const Philox4 k1 = b2g_philox(seed_lo, seed_hi, (uint32_t)c, (uint32_t)(c >> 32), B2G_STREAM_PERM, 1);
-    const uint32_t keys[8] = {k0.x, k0.y, k0.z, k0.w, k1.x, k1.y, k1.z, k1.w};
-    const uint32_t mask = (1u << half_bits) - 1u;
-    uint64_t x = (uint64_t)i;
-    do {
-        uint32_t L = (uint32_t)(x >> half_bits) & mask, R = (uint32_t)x & mask;
-#pragma unroll
-        for (int r = 0; r < 8; ++r) {
-            const uint32_t f = mix32(R ^ keys[r]) & mask;
-            const uint32_t nl = R;
-            R = L ^ f;
-            L = nl;
-        }
-        x = ((uint64_t)L << half_bits) | R;
-    } while (x >= (uint64_t)n);
-    out[i] = (int32_t)x;
+    uint32_t keys[8];
+    b2g_perm_keys(seed_lo, seed_hi, c, keys);
+    out[i] = (int32_t)b2g_perm_apply(keys, half_bits, (uint64_t)n, (uint64_t)i);
 }
 
 extern "C" int b2g_permutation(uint64_t seed, const unsigned long long* counter_dev,
@@ -207,9 +185,7 @@ extern "C" int b2g_permutation(uint64_t seed, const unsigned long long* counter_
     B2G_CHECK_ARG(n >= 0 && n <= 0x7fffffff, "n out of range for int32 ids");
     if (n == 0) return B2G_OK;
     B2G_CHECK_ARG(out != nullptr, "NULL pointer");
-    int bits = 1;
-    while (((int64_t)1 << bits) < n) ++bits;
-    const int half_bits = (bits + 1) / 2 < 1 ? 1 : (bits + 1) / 2;
+    const int half_bits = b2g_perm_half_bits(n);
     permutation_kernel<<<(unsigned)((n + 255) / 256), 256, 0, (cudaStream_t)stream>>>(
         (uint32_t)seed, (uint32_t)(seed >> 32), counter_dev, counter, n, half_bits, out);
     B2G_CHECK_LAUNCH();

@@ -73,6 +73,8 @@ static int launch_mlp_tc(const MlpArgs& a, cudaStream_t s) {
     if (!configured) {
         B2G_CUDA(cudaFuncSetAttribute(tc::mlp_train_tc_kernel<O, A>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                       (int)smem));
+        B2G_CUDA(cudaFuncSetAttribute(tc::mlp_train_tc_kernel<O, A>, cudaFuncAttributePreferredSharedMemoryCarveout,
+                                      cudaSharedmemCarveoutMaxShared));
         configured = true;
     }
     tc::mlp_train_tc_kernel<O, A><<<mlp_tc_grid(a.mb), tc::NT, smem, s>>>(a);

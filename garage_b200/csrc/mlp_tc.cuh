@@ -221,12 +221,13 @@ struct Small {  // float offsets inside the small region
 template <int O, int A>
 constexpr size_t smem_bytes() { return OFF_SMALL + sizeof(float) * Small<O, A>::END; }
 
-// minibatch row id of (tile, row) or -1 past the end
-__device__ __forceinline__ int64_t tile_src(const MlpArgs& a, int64_t tile, int64_t ntiles, int r) {
-    if (tile >= ntiles) return -1;
-    const int64_t m = tile * R + r;
+// minibatch row id of row m of the minibatch, or -1 past its end: supplied index list,
+// on-the-fly Feistel permutation (b2g_perm_apply, same ids as b2g_permutation), or sequential
+__device__ __forceinline__ int64_t mb_src(const MlpArgs& a, int64_t m) {
     if (m >= a.mb) return -1;
-    return a.idx ? (int64_t)a.idx[m] : (a.start + m);
+    if (a.idx) return (int64_t)a.idx[m];
+    if (a.perm_n > 0) return (int64_t)b2g_perm_apply(a.perm_keys, a.perm_half_bits, (uint64_t)a.perm_n, (uint64_t)(a.start + m));
+    return a.start + m;
 }
 
 template <int O, int A>
@@ -256,423 +257,483 @@ __device__ __forceinline__ RowData<O, A> load_row(const MlpArgs& a, int64_t src)
     return d;
 }
 
+// One CTA's state: shared-memory carve-up, TMEM base, thread roles and the register accumulators.
+// Used by the one-minibatch kernel below and by the persistent training loop (train_loop.cu).
 template <int O, int A>
-__global__ void __launch_bounds__(NT, 2) mlp_train_tc_kernel(const MlpArgs a) {
+struct Cta {
     static_assert(O <= 4 && A <= 4, "aug panel holds [1 | x] in 8 columns; obs staged as float4");
     using S = Small<O, A>;
-    constexpr int NIN = S::NIN;
-    const MlpLayout L{O, H, A};
-    const int P = L.total();
-    extern __shared__ __align__(1024) uint8_t smem[];
-    float* sm = reinterpret_cast<float*>(smem + OFF_SMALL);
-    float *sW1 = sm + S::W1, *sB1 = sm + S::B1, *sB2 = sm + S::B2, *sW3 = sm + S::W3, *sB3 = sm + S::B3,
-          *sX = sm + S::X, *sMu = sm + S::MU, *sIn = sm + S::IN;
-    int64_t* sSrc = reinterpret_cast<int64_t*>(sm + S::SRC);
-    uint32_t* tslot = reinterpret_cast<uint32_t*>(sm + S::TSLOT);
-    const uint32_t sb = smem_u32(smem);
-    const uint32_t bar1 = smem_u32(sm + S::BARS), bar2 = bar1 + 8, bar3 = bar1 + 16, bar4 = bar1 + 24;
-    const int tid = threadIdx.x, w = __shfl_sync(0xffffffffu, tid >> 5, 0), l = tid & 31;  // w: provably warp-uniform
-    const int64_t ntiles = (a.mb + R - 1) / R;
-#define TC_STAMP(i) do { if (a.timing && tid == 0 && (i) < 32) a.timing[blockIdx.x * 32 + (i)] = clock64(); } while (0)
-    TC_STAMP(0);
+    static constexpr int NIN = S::NIN;
+    uint8_t* smem;
+    float *sm, *sW1, *sB1, *sB2, *sW3, *sB3, *sX, *sMu, *sIn;
+    int64_t* sSrc;
+    uint32_t sb, bar1, bar2, bar3, bar4, tmem, tiles_done;
+    int tid, w, l, q4, hf, g, p, ra, rb, c0;
+    bool first;  // no MMA has written the G/F accumulators since the last readout
+    MlpDist dist;
+    float gW3[A][8], gB3[A];
+    MlpRowAcc racc;
+    long long* stamps;
 
-    // ---- gather pipeline (threads 0..R-1 own one row): row ids run two tiles ahead of the
-    // tile being computed, row data one tile ahead, so no stage waits on a dependent load
-    int64_t src_n = -1, src_nn = -1;
-    RowData<O, A> row_n;
-    if (tid < R) {
-        src_n = tile_src(a, blockIdx.x, ntiles, tid);
-        src_nn = tile_src(a, (int64_t)blockIdx.x + gridDim.x, ntiles, tid);
-        row_n = load_row<O, A>(a, src_n);
+    __device__ __forceinline__ void stamp(int i) const {
+        if (stamps && tid == 0 && i < 32) stamps[i] = clock64();
     }
 
-    // ---- one-time setup: barriers, TMEM, weights (W2 as hi/lo panels, the rest fp32)
-    if (tid == 0) {
-        if (sb & 1023u) __trap();
+    // barriers + TMEM allocation; every thread of the CTA calls it once
+    __device__ __forceinline__ void init(uint8_t* smem_) {
+        smem = smem_;
+        sm = reinterpret_cast<float*>(smem + OFF_SMALL);
+        sW1 = sm + S::W1; sB1 = sm + S::B1; sB2 = sm + S::B2; sW3 = sm + S::W3; sB3 = sm + S::B3;
+        sX = sm + S::X; sMu = sm + S::MU; sIn = sm + S::IN;
+        sSrc = reinterpret_cast<int64_t*>(sm + S::SRC);
+        uint32_t* tslot = reinterpret_cast<uint32_t*>(sm + S::TSLOT);
+        sb = smem_u32(smem);
+        bar1 = smem_u32(sm + S::BARS); bar2 = bar1 + 8; bar3 = bar1 + 16; bar4 = bar1 + 24;
+        tid = threadIdx.x;
+        w = __shfl_sync(0xffffffffu, tid >> 5, 0);  // provably warp-uniform
+        l = tid & 31;
+        q4 = w & 3; hf = w >> 2; g = l >> 2; p = l & 3;
+        ra = 16 * q4 + g; rb = ra + 8; c0 = 32 * hf;
+        tiles_done = 0;
+        first = true;
+        stamps = nullptr;
+        if (tid == 0) {
+            if (sb & 1023u) __trap();
 #pragma unroll
-        for (int i = 0; i < 4; ++i) asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(bar1 + 8 * i));
-        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+            for (int i = 0; i < 4; ++i) asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(bar1 + 8 * i));
+            asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        }
+        if (w == 1) {
+            asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], 256;" ::"r"(smem_u32(tslot)) : "memory");
+            asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+        }
+        for (int i = tid; i < (int)(PANEL / 16); i += NT)  // aug panel: columns 16..31 are never written
+            reinterpret_cast<float4*>(smem + OFF_ACT + 2 * PANEL)[i] = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+        tc_before_sync();
+        __syncthreads();
+        tc_after_sync();
+        tmem = __shfl_sync(0xffffffffu, *tslot, 0);
     }
-    if (w == 1) {
-        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], 256;" ::"r"(smem_u32(tslot)) : "memory");
-        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+
+    __device__ __forceinline__ void fini() {
+        tc_before_sync();
+        __syncthreads();
+        if (w == 1) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, 256;" ::"r"(tmem) : "memory");
     }
-    {
-        const float* w2 = a.params + L.off_w2();  // 4-byte aligned only (offset 1 + H*O + H floats)
-        float v[4][4];
+
+    // W2 as tf32 hi/lo panels, the small layers as fp32; call with no MMA in flight.
+    // `ld` loads one parameter (plain or L2-coherent, the training loop rewrites them)
+    template <class Ld>
+    __device__ __forceinline__ void load_weights(const MlpArgs& a, const float* params, Ld ld) {
+        const MlpLayout L{O, H, A};
+        {
+            const float* w2 = params + L.off_w2();  // 4-byte aligned only (offset 1 + H*O + H floats)
+            float v[4][4];
+#pragma unroll
+            for (int i = 0; i < 4; ++i)
+#pragma unroll
+                for (int j = 0; j < 4; ++j) v[i][j] = ld(w2 + (tid + NT * i) * 4 + j);
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+                const int e = (tid + NT * i) * 4, c = e >> 6, k = e & 63;
+                const uint32_t off = (uint32_t)(k >> 5) * WPANEL + chunk_off(c, (k & 31) >> 2);
+                store_split4(smem + OFF_W, smem + OFF_W + 2 * WPANEL, off, v[i]);
+            }
+        }
+        for (int i = tid; i < H * O; i += NT) sW1[i] = ld(params + L.off_w1() + i);
+        if (tid < H) {
+            sB1[tid] = ld(params + L.off_b1() + tid);
+            sB2[tid] = ld(params + L.off_b2() + tid);
+        }
+        for (int i = tid; i < A * H; i += NT) sW3[i] = ld(params + L.off_w3() + i);
+        if (tid < A) sB3[tid] = ld(params + L.off_b3() + tid);
+        dist = mlp_dist(a, ld(params + L.off_logstd()));
+        fence_async_smem();
+        __syncthreads();
+    }
+
+    __device__ __forceinline__ void zero_acc() {
+#pragma unroll
+        for (int q = 0; q < A; ++q) {
+            gB3[q] = 0.0f;
+#pragma unroll
+            for (int c = 0; c < 8; ++c) gW3[q][c] = 0.0f;
+        }
+        racc = MlpRowAcc{};
+    }
+
+    // forward + loss + backward of the 64-row tiles tile0, tile0 + stride, ... of minibatch `a`;
+    // gradients accumulate in TMEM (G, F) and registers until write_partial()
+    __device__ __forceinline__ void run_tiles(const MlpArgs& a, int64_t tile0, int64_t stride) {
+        const int64_t ntiles = (a.mb + R - 1) / R;
+        const uint32_t tfrag = tmem + ((uint32_t)(32 * q4) << 16) + TM_D + c0;
+        uint8_t* const act_hi = smem + OFF_ACT + hf * PANEL;
+        uint8_t* const act_lo = smem + OFF_ACT + (3 + hf) * PANEL;
+        uint8_t* const dz_hi = smem + OFF_DZ + hf * PANEL;
+        uint8_t* const dz_lo = smem + OFF_DZ + (2 + hf) * PANEL;
+        float w3c[A][8], b2c[8];  // this thread's columns of W3 and b2
 #pragma unroll
         for (int i = 0; i < 4; ++i)
 #pragma unroll
-            for (int j = 0; j < 4; ++j) v[i][j] = __ldg(w2 + (tid + NT * i) * 4 + j);
+            for (int e = 0; e < 2; ++e) {
+                const int c = c0 + 8 * i + 2 * p + e;
+                b2c[2 * i + e] = sB2[c];
 #pragma unroll
-        for (int i = 0; i < 4; ++i) {
-            const int e = (tid + NT * i) * 4, c = e >> 6, k = e & 63;
-            const uint32_t off = (uint32_t)(k >> 5) * WPANEL + chunk_off(c, (k & 31) >> 2);
-            store_split4(smem + OFF_W, smem + OFF_W + 2 * WPANEL, off, v[i]);
-        }
-    }
-    for (int i = tid; i < (int)(PANEL / 16); i += NT)  // aug panel: columns 16..31 are never written
-        reinterpret_cast<float4*>(smem + OFF_ACT + 2 * PANEL)[i] = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
-    for (int i = tid; i < H * O; i += NT) sW1[i] = a.params[L.off_w1() + i];
-    if (tid < H) {
-        sB1[tid] = a.params[L.off_b1() + tid];
-        sB2[tid] = a.params[L.off_b2() + tid];
-    }
-    for (int i = tid; i < A * H; i += NT) sW3[i] = a.params[L.off_w3() + i];
-    if (tid < A) sB3[tid] = a.params[L.off_b3() + tid];
-    const MlpDist dist = mlp_dist(a, a.params[L.off_logstd()]);
-    if (a.step_counter && blockIdx.x == 0 && tid == 0) *a.step_counter += 1ull;
-    fence_async_smem();
-    tc_before_sync();
-    __syncthreads();
-    tc_after_sync();
-    const uint32_t tmem = __shfl_sync(0xffffffffu, *tslot, 0);
-    TC_STAMP(1);
-
-    // ---- epilogue role: rows ra = 16q + g and rb = ra + 8, feature pairs 32hf + 8i + 2p (+1)
-    const int q4 = w & 3, hf = w >> 2, g = l >> 2, p = l & 3;
-    const int ra = 16 * q4 + g, rb = ra + 8, c0 = 32 * hf;
-    const uint32_t tfrag = tmem + ((uint32_t)(32 * q4) << 16) + TM_D + c0;
-    float gW3[A][8], gB3[A];
-    MlpRowAcc racc{};
-#pragma unroll
-    for (int q = 0; q < A; ++q) {
-        gB3[q] = 0.0f;
-#pragma unroll
-        for (int c = 0; c < 8; ++c) gW3[q][c] = 0.0f;
-    }
-    uint8_t* const act_hi = smem + OFF_ACT + hf * PANEL;
-    uint8_t* const act_lo = smem + OFF_ACT + (3 + hf) * PANEL;
-    uint8_t* const dz_hi = smem + OFF_DZ + hf * PANEL;
-    uint8_t* const dz_lo = smem + OFF_DZ + (2 + hf) * PANEL;
-    float w3c[A][8], b2c[8];  // this thread's columns of W3 and b2
-#pragma unroll
-    for (int i = 0; i < 4; ++i)
-#pragma unroll
-        for (int e = 0; e < 2; ++e) {
-            const int c = c0 + 8 * i + 2 * p + e;
-            b2c[2 * i + e] = sB2[c];
-#pragma unroll
-            for (int q = 0; q < A; ++q) w3c[q][2 * i + e] = sW3[q * H + c];
-        }
-
-    uint32_t it = 0;
-    for (int64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++it) {
-        const uint32_t par = it & 1;
-        const int64_t m0 = tile * R;
-        const int valid = (int)((a.mb - m0) < R ? (a.mb - m0) : R);
-        const int nks = (valid + 7) >> 3;
-        if (it > 0) mbar_wait(bar4, par ^ 1);  // every MMA of the previous tile has drained
-        TC_STAMP(2 + 10 * it);
-        // ---- publish this tile's rows; aug panel row = [1 x_hi 0.. | 0 x_lo 0..]; prefetch ahead
-        if (tid < R) {
-            sSrc[tid] = src_n;
-            float xh[8], xl[8];
-#pragma unroll
-            for (int i = 0; i < 8; ++i) { xh[i] = 0.0f; xl[i] = 0.0f; }
-            xh[0] = 1.0f;
-#pragma unroll
-            for (int o = 0; o < O; ++o) split_tf32(row_n.x[o], xh[1 + o], xl[1 + o]);
-            *reinterpret_cast<float4*>(sX + tid * 4) = make_float4(row_n.x[0], row_n.x[1], row_n.x[2], row_n.x[3]);
-#pragma unroll
-            for (int i = 0; i < NIN; ++i) sIn[tid * NIN + i] = row_n.in[i];
-            uint8_t* aug = smem + OFF_ACT + 2 * PANEL;
-            const uint32_t o0 = chunk_off(tid, 0), o1 = chunk_off(tid, 2);
-            *reinterpret_cast<float4*>(aug + o0) = make_float4(xh[0], xh[1], xh[2], xh[3]);
-            *reinterpret_cast<float4*>(aug + o0 + 16) = make_float4(xh[4], xh[5], xh[6], xh[7]);
-            *reinterpret_cast<float4*>(aug + o1) = make_float4(xl[0], xl[1], xl[2], xl[3]);
-            *reinterpret_cast<float4*>(aug + o1 + 16) = make_float4(xl[4], xl[5], xl[6], xl[7]);
-            src_n = src_nn;
-            row_n = load_row<O, A>(a, src_n);
-            src_nn = tile_src(a, tile + 2 * (int64_t)gridDim.x, ntiles, tid);
-        }
-        __syncthreads();
-        TC_STAMP(3 + 10 * it);
-        // ---- L1: h1 = tanh(W1 x + b1); a quarter-warp writes the 8 chunks of one row (conflict-free)
-        {
-            const int pn = w & 1, rbk = w >> 1, j = l & 7, rs = l >> 3, f0 = 32 * pn + 4 * j;
-            float w1[4][O], bb[4];
-#pragma unroll
-            for (int q = 0; q < 4; ++q) {
-                bb[q] = sB1[f0 + q];
-#pragma unroll
-                for (int o = 0; o < O; ++o) w1[q][o] = sW1[(f0 + q) * O + o];
+                for (int q = 0; q < A; ++q) w3c[q][2 * i + e] = sW3[q * H + c];
             }
-            uint8_t* hp = smem + OFF_ACT + pn * PANEL;
-            uint8_t* lp = smem + OFF_ACT + (3 + pn) * PANEL;
+        // gather pipeline (threads 0..R-1 own one row): row ids run two tiles ahead of the tile
+        // being computed, row data one tile ahead, so no stage waits on a dependent load
+        int64_t src_n = -1, src_nn = -1;
+        RowData<O, A> row_n;
+        if (tid < R) {
+            src_n = tile0 < ntiles ? mb_src(a, tile0 * R + tid) : -1;
+            src_nn = tile0 + stride < ntiles ? mb_src(a, (tile0 + stride) * R + tid) : -1;
+            row_n = load_row<O, A>(a, src_n);
+        }
+        int it = 0;
+        for (int64_t tile = tile0; tile < ntiles; tile += stride, ++it) {
+            const uint32_t par = tiles_done & 1;
+            const int64_t m0 = tile * R;
+            const int valid = (int)((a.mb - m0) < R ? (a.mb - m0) : R);
+            const int nks = (valid + 7) >> 3;
+            if (tiles_done > 0) mbar_wait(bar4, par ^ 1);  // every MMA of the previous tile has drained
+            stamp(2 + 10 * it);
+            // ---- publish this tile's rows; aug panel row = [1 x_hi 0.. | 0 x_lo 0..]; prefetch ahead
+            if (tid < R) {
+                sSrc[tid] = src_n;
+                float xh[8], xl[8];
 #pragma unroll
-            for (int i = 0; i < 4; ++i) {
-                const int r = 16 * rbk + rs + 4 * i;
-                const float4 xv = *reinterpret_cast<const float4*>(sX + r * 4);
-                const float x[4] = {xv.x, xv.y, xv.z, xv.w};
-                float h[4];
+                for (int i = 0; i < 8; ++i) { xh[i] = 0.0f; xl[i] = 0.0f; }
+                xh[0] = 1.0f;
+#pragma unroll
+                for (int o = 0; o < O; ++o) split_tf32(row_n.x[o], xh[1 + o], xl[1 + o]);
+                *reinterpret_cast<float4*>(sX + tid * 4) = make_float4(row_n.x[0], row_n.x[1], row_n.x[2], row_n.x[3]);
+#pragma unroll
+                for (int i = 0; i < NIN; ++i) sIn[tid * NIN + i] = row_n.in[i];
+                uint8_t* aug = smem + OFF_ACT + 2 * PANEL;
+                const uint32_t o0 = chunk_off(tid, 0), o1 = chunk_off(tid, 2);
+                *reinterpret_cast<float4*>(aug + o0) = make_float4(xh[0], xh[1], xh[2], xh[3]);
+                *reinterpret_cast<float4*>(aug + o0 + 16) = make_float4(xh[4], xh[5], xh[6], xh[7]);
+                *reinterpret_cast<float4*>(aug + o1) = make_float4(xl[0], xl[1], xl[2], xl[3]);
+                *reinterpret_cast<float4*>(aug + o1 + 16) = make_float4(xl[4], xl[5], xl[6], xl[7]);
+                src_n = src_nn;
+                row_n = load_row<O, A>(a, src_n);
+                const int64_t t2 = tile + 2 * stride;
+                src_nn = t2 < ntiles ? mb_src(a, t2 * R + tid) : -1;
+            }
+            __syncthreads();
+            stamp(3 + 10 * it);
+            // ---- L1: h1 = tanh(W1 x + b1); a quarter-warp writes the 8 chunks of one row (conflict-free)
+            {
+                const int pn = w & 1, rbk = w >> 1, j = l & 7, rs = l >> 3, f0 = 32 * pn + 4 * j;
+                float w1[4][O], bb[4];
 #pragma unroll
                 for (int q = 0; q < 4; ++q) {
-                    float z = bb[q];
+                    bb[q] = sB1[f0 + q];
 #pragma unroll
-                    for (int o = 0; o < O; ++o) z = fmaf(w1[q][o], x[o], z);
-                    h[q] = TC_TANH(z);
+                    for (int o = 0; o < O; ++o) w1[q][o] = sW1[(f0 + q) * O + o];
                 }
-                store_split4(hp, lp, chunk_off(r, j), h);
-            }
-        }
-        TC_STAMP(4 + 10 * it);
-        fence_async_smem();
-        __syncthreads();
-        if (it == 0) TC_STAMP(22);
-        if (w == 0) {  // descriptors stay in uniform registers: the whole warp takes the branch
-            tc_after_sync();
-            if (elect_one()) {
-                issue_gemm1(sb, tmem);
-                umma_commit(bar1);
-            }
-            __syncwarp();
-        }
-        TC_STAMP(5 + 10 * it);
-        mbar_wait(bar1, par);
-        tc_after_sync();
-        TC_STAMP(6 + 10 * it);
-        // ---- EPI1: h2, mu, loss, dz2
-        float h2[16];  // [4i + 2*row + e]
-        {
-            float z[16];
-            tmem_ld_frag(tfrag, z);
-            float mpa[A], mpb[A];
+                uint8_t* hp = smem + OFF_ACT + pn * PANEL;
+                uint8_t* lp = smem + OFF_ACT + (3 + pn) * PANEL;
 #pragma unroll
-            for (int q = 0; q < A; ++q) { mpa[q] = 0.0f; mpb[q] = 0.0f; }
+                for (int i = 0; i < 4; ++i) {
+                    const int r = 16 * rbk + rs + 4 * i;
+                    const float4 xv = *reinterpret_cast<const float4*>(sX + r * 4);
+                    const float x[4] = {xv.x, xv.y, xv.z, xv.w};
+                    float h[4];
 #pragma unroll
-            for (int i = 0; i < 4; ++i)
+                    for (int q = 0; q < 4; ++q) {
+                        float z = bb[q];
 #pragma unroll
-                for (int e = 0; e < 2; ++e) {
-                    const float ha = TC_TANH(z[4 * i + e] + b2c[2 * i + e]);
-                    const float hb = TC_TANH(z[4 * i + 2 + e] + b2c[2 * i + e]);
-                    h2[4 * i + e] = ha;
-                    h2[4 * i + 2 + e] = hb;
-#pragma unroll
-                    for (int q = 0; q < A; ++q) {
-                        mpa[q] = fmaf(w3c[q][2 * i + e], ha, mpa[q]);
-                        mpb[q] = fmaf(w3c[q][2 * i + e], hb, mpb[q]);
+                        for (int o = 0; o < O; ++o) z = fmaf(w1[q][o], x[o], z);
+                        h[q] = TC_TANH(z);
                     }
-                }
-#pragma unroll
-            for (int q = 0; q < A; ++q) {
-                mpa[q] += __shfl_xor_sync(0xffffffffu, mpa[q], 1);
-                mpb[q] += __shfl_xor_sync(0xffffffffu, mpb[q], 1);
-                mpa[q] += __shfl_xor_sync(0xffffffffu, mpa[q], 2);
-                mpb[q] += __shfl_xor_sync(0xffffffffu, mpb[q], 2);
-                if (p == 0) {
-                    sMu[(hf * A + q) * R + ra] = mpa[q];
-                    sMu[(hf * A + q) * R + rb] = mpb[q];
+                    store_split4(hp, lp, chunk_off(r, j), h);
                 }
             }
-        }
-        __syncthreads();
-        {
-            // the loss of a row is evaluated by the lanes p and p^2 of its quad (p&1 picks the row),
-            // then handed to the other lanes: half the instructions of evaluating both rows everywhere
-            float dmu[2][A];
+            stamp(4 + 10 * it);
+            fence_async_smem();
+            __syncthreads();
+            if (w == 0) {  // descriptors stay in uniform registers: the whole warp takes the branch
+                tc_after_sync();
+                if (elect_one()) {
+                    issue_gemm1(sb, tmem);
+                    umma_commit(bar1);
+                }
+                __syncwarp();
+            }
+            stamp(5 + 10 * it);
+            mbar_wait(bar1, par);
+            tc_after_sync();
+            stamp(6 + 10 * it);
+            // ---- EPI1: h2, mu, loss, dz2
+            float h2[16];  // [4i + 2*row + e]
             {
-                const int r = (p & 1) ? rb : ra;
-                float mu[A], dm[A];
+                float z[16];
+                tmem_ld_frag(tfrag, z);
+                float mpa[A], mpb[A];
 #pragma unroll
-                for (int q = 0; q < A; ++q) {
-                    mu[q] = sB3[q] + sMu[q * R + r] + sMu[(A + q) * R + r];
-                    dm[q] = 0.0f;
-                }
-                if (sSrc[r] >= 0) {
-                    MlpRowIn<A> in;
+                for (int q = 0; q < A; ++q) { mpa[q] = 0.0f; mpb[q] = 0.0f; }
 #pragma unroll
-                    for (int q = 0; q < A; ++q) { in.act[q] = sIn[r * NIN + q]; in.old_mean[q] = 0.0f; }
-                    in.adv = sIn[r * NIN + A]; in.old_logp = sIn[r * NIN + A + 1]; in.ret = sIn[r * NIN + A + 2];
-                    mlp_row_loss<A>(a, in, mu, dist, dm, racc);
-                }
-#pragma unroll
-                for (int q = 0; q < A; ++q) {
-                    gB3[q] += dm[q];
-                    dmu[0][q] = __shfl_sync(0xffffffffu, dm[q], l & ~3);
-                    dmu[1][q] = __shfl_sync(0xffffffffu, dm[q], (l & ~3) | 1);
-                }
-            }
-#pragma unroll
-            for (int i = 0; i < 4; ++i) {
-                float dz[4];  // [2*row + e]
-#pragma unroll
-                for (int s = 0; s < 2; ++s)
+                for (int i = 0; i < 4; ++i)
 #pragma unroll
                     for (int e = 0; e < 2; ++e) {
-                        const float h = h2[4 * i + 2 * s + e];
-                        float dh = 0.0f;
+                        const float ha = TC_TANH(z[4 * i + e] + b2c[2 * i + e]);
+                        const float hb = TC_TANH(z[4 * i + 2 + e] + b2c[2 * i + e]);
+                        h2[4 * i + e] = ha;
+                        h2[4 * i + 2 + e] = hb;
 #pragma unroll
                         for (int q = 0; q < A; ++q) {
-                            dh = fmaf(w3c[q][2 * i + e], dmu[s][q], dh);
-                            gW3[q][2 * i + e] = fmaf(dmu[s][q], h, gW3[q][2 * i + e]);
+                            mpa[q] = fmaf(w3c[q][2 * i + e], ha, mpa[q]);
+                            mpb[q] = fmaf(w3c[q][2 * i + e], hb, mpb[q]);
                         }
-                        dz[2 * s + e] = dh * (1.0f - h * h);
                     }
-                store_split2(dz_hi, dz_lo, pair_off(ra, i, p), dz[0], dz[1]);
-                store_split2(dz_hi, dz_lo, pair_off(rb, i, p), dz[2], dz[3]);
-            }
-        }
-        TC_STAMP(7 + 10 * it);
-        fence_async_smem();
-        tc_before_sync();
-        __syncthreads();
-        if (it == 0) TC_STAMP(23);
-        if (w == 0) {
-            tc_after_sync();
-            if (elect_one()) {
-                issue_gemm2(sb, tmem);
-                umma_commit(bar2);
-                if (it == 0 && a.timing) a.timing[blockIdx.x * 32 + 24] = clock64();
-                issue_gemm3(sb, tmem, it == 0, nks);
-                umma_commit(bar3);
-            }
-            __syncwarp();
-        }
-        // ---- EPI2: dz1 = dh1 (1 - h1^2)
-        TC_STAMP(8 + 10 * it);
-        mbar_wait(bar2, par);
-        tc_after_sync();
-        TC_STAMP(9 + 10 * it);
-        {
-            float d[16];
-            tmem_ld_frag(tfrag, d);
 #pragma unroll
-            for (int i = 0; i < 4; ++i)
-#pragma unroll
-                for (int s = 0; s < 2; ++s) {
-                    const uint32_t off = pair_off(s ? rb : ra, i, p);
-                    const float2 hh = *reinterpret_cast<const float2*>(act_hi + off);
-                    const float2 hl = *reinterpret_cast<const float2*>(act_lo + off);
-                    const float h0 = hh.x + hl.x, h1 = hh.y + hl.y;
-                    d[4 * i + 2 * s] *= (1.0f - h0 * h0);
-                    d[4 * i + 2 * s + 1] *= (1.0f - h1 * h1);
+                for (int q = 0; q < A; ++q) {
+                    mpa[q] += __shfl_xor_sync(0xffffffffu, mpa[q], 1);
+                    mpb[q] += __shfl_xor_sync(0xffffffffu, mpb[q], 1);
+                    mpa[q] += __shfl_xor_sync(0xffffffffu, mpa[q], 2);
+                    mpb[q] += __shfl_xor_sync(0xffffffffu, mpb[q], 2);
+                    if (p == 0) {
+                        sMu[(hf * A + q) * R + ra] = mpa[q];
+                        sMu[(hf * A + q) * R + rb] = mpb[q];
+                    }
                 }
-            mbar_wait(bar3, par);  // GEMM3 still reads dz2 from the DZ panels
-            TC_STAMP(10 + 10 * it);
-#pragma unroll
-            for (int i = 0; i < 4; ++i) {
-                store_split2(dz_hi, dz_lo, pair_off(ra, i, p), d[4 * i], d[4 * i + 1]);
-                store_split2(dz_hi, dz_lo, pair_off(rb, i, p), d[4 * i + 2], d[4 * i + 3]);
             }
-        }
-        fence_async_smem();
-        tc_before_sync();
-        __syncthreads();
-        if (w == 0) {
+            __syncthreads();
+            {
+                // the loss of a row is evaluated by the lanes p and p^2 of its quad (p&1 picks the row),
+                // then handed to the other lanes: half the instructions of evaluating both rows everywhere
+                float dmu[2][A];
+                {
+                    const int r = (p & 1) ? rb : ra;
+                    float mu[A], dm[A];
+#pragma unroll
+                    for (int q = 0; q < A; ++q) {
+                        mu[q] = sB3[q] + sMu[q * R + r] + sMu[(A + q) * R + r];
+                        dm[q] = 0.0f;
+                    }
+                    if (sSrc[r] >= 0) {
+                        MlpRowIn<A> in;
+#pragma unroll
+                        for (int q = 0; q < A; ++q) { in.act[q] = sIn[r * NIN + q]; in.old_mean[q] = 0.0f; }
+                        in.adv = sIn[r * NIN + A]; in.old_logp = sIn[r * NIN + A + 1]; in.ret = sIn[r * NIN + A + 2];
+                        mlp_row_loss<A>(a, in, mu, dist, dm, racc);
+                    }
+#pragma unroll
+                    for (int q = 0; q < A; ++q) {
+                        gB3[q] += dm[q];
+                        dmu[0][q] = __shfl_sync(0xffffffffu, dm[q], l & ~3);
+                        dmu[1][q] = __shfl_sync(0xffffffffu, dm[q], (l & ~3) | 1);
+                    }
+                }
+#pragma unroll
+                for (int i = 0; i < 4; ++i) {
+                    float dz[4];  // [2*row + e]
+#pragma unroll
+                    for (int s = 0; s < 2; ++s)
+#pragma unroll
+                        for (int e = 0; e < 2; ++e) {
+                            const float h = h2[4 * i + 2 * s + e];
+                            float dh = 0.0f;
+#pragma unroll
+                            for (int q = 0; q < A; ++q) {
+                                dh = fmaf(w3c[q][2 * i + e], dmu[s][q], dh);
+                                gW3[q][2 * i + e] = fmaf(dmu[s][q], h, gW3[q][2 * i + e]);
+                            }
+                            dz[2 * s + e] = dh * (1.0f - h * h);
+                        }
+                    store_split2(dz_hi, dz_lo, pair_off(ra, i, p), dz[0], dz[1]);
+                    store_split2(dz_hi, dz_lo, pair_off(rb, i, p), dz[2], dz[3]);
+                }
+            }
+            stamp(7 + 10 * it);
+            fence_async_smem();
+            tc_before_sync();
+            __syncthreads();
+            if (w == 0) {
+                tc_after_sync();
+                if (elect_one()) {
+                    issue_gemm2(sb, tmem);
+                    umma_commit(bar2);
+                    issue_gemm3(sb, tmem, first, nks);
+                    umma_commit(bar3);
+                }
+                __syncwarp();
+            }
+            // ---- EPI2: dz1 = dh1 (1 - h1^2)
+            stamp(8 + 10 * it);
+            mbar_wait(bar2, par);
             tc_after_sync();
-            if (elect_one()) {
-                issue_gemm4(sb, tmem, it == 0, nks);
-                umma_commit(bar4);
+            stamp(9 + 10 * it);
+            {
+                float d[16];
+                tmem_ld_frag(tfrag, d);
+#pragma unroll
+                for (int i = 0; i < 4; ++i)
+#pragma unroll
+                    for (int s = 0; s < 2; ++s) {
+                        const uint32_t off = pair_off(s ? rb : ra, i, p);
+                        const float2 hh = *reinterpret_cast<const float2*>(act_hi + off);
+                        const float2 hl = *reinterpret_cast<const float2*>(act_lo + off);
+                        const float h0 = hh.x + hl.x, h1 = hh.y + hl.y;
+                        d[4 * i + 2 * s] *= (1.0f - h0 * h0);
+                        d[4 * i + 2 * s + 1] *= (1.0f - h1 * h1);
+                    }
+                mbar_wait(bar3, par);  // GEMM3 still reads dz2 from the DZ panels
+                stamp(10 + 10 * it);
+#pragma unroll
+                for (int i = 0; i < 4; ++i) {
+                    store_split2(dz_hi, dz_lo, pair_off(ra, i, p), d[4 * i], d[4 * i + 1]);
+                    store_split2(dz_hi, dz_lo, pair_off(rb, i, p), d[4 * i + 2], d[4 * i + 3]);
+                }
             }
-            __syncwarp();
+            fence_async_smem();
+            tc_before_sync();
+            __syncthreads();
+            if (w == 0) {
+                tc_after_sync();
+                if (elect_one()) {
+                    issue_gemm4(sb, tmem, first, nks);
+                    umma_commit(bar4);
+                }
+                __syncwarp();
+            }
+            first = false;
+            ++tiles_done;
+            stamp(11 + 10 * it);
         }
-        TC_STAMP(11 + 10 * it);
     }
-    TC_STAMP(28);
-    mbar_wait(bar4, (it - 1) & 1);
-    tc_after_sync();
-    TC_STAMP(29);
 
-    // ---- write this CTA's partial: [P gradients | MLP_NSTATS statistics]
-    float* out = a.partial + (int64_t)blockIdx.x * (P + MLP_NSTATS);
-    float* scr = reinterpret_cast<float*>(smem + OFF_ACT);
-    constexpr int SW = 81;  // scratch row stride (odd: conflict-free)
-    const uint32_t tlane = tmem + ((uint32_t)(32 * q4) << 16);
-    // every lane folds its own hi/lo column groups; lanes 64..127 (the lo-split rows) park the
-    // result in smem, lanes 0..63 add theirs, then every thread stores coalesced
-    if (tid < 128) {
-        const int m = tid & 63;
-        const bool lo_rows = tid >= 64;
+    // drain the MMAs, fold G/F/register accumulators into this CTA's partial row
+    // [P gradients | MLP_NSTATS statistics]; afterwards the accumulators start from zero again
+    __device__ __forceinline__ void write_partial(float* out, bool with_stats) {
+        const MlpLayout L{O, H, A};
+        const int P = L.total();
+        stamp(28);
+        if (tiles_done > 0) mbar_wait(bar4, (tiles_done - 1) & 1);
+        tc_after_sync();
+        stamp(29);
+        float* scr = reinterpret_cast<float*>(smem + OFF_ACT);
+        constexpr int SW = 81;  // scratch row stride (odd: conflict-free)
+        const uint32_t tlane = tmem + ((uint32_t)(32 * q4) << 16);
+        if (first) {  // this CTA had no tile: its partial is zero
+            for (int e = tid; e < P + MLP_NSTATS; e += NT) out[e] = 0.0f;
+            __syncthreads();
+            return;
+        }
+        // every lane folds its own hi/lo column groups; lanes 64..127 (the lo-split rows) park the
+        // result in smem, lanes 0..63 add theirs, then every thread stores coalesced
+        if (tid < 128) {
+            const int m = tid & 63;
+            const bool lo_rows = tid >= 64;
 #pragma unroll
-        for (int gq = 0; gq < 4; ++gq) {
-            float v[16], u[16];
-            tmem_ld16(tlane + TM_G + 16 * gq, v);
-            tmem_ld16(tlane + TM_G + 96 + 16 * gq, u);
+            for (int gq = 0; gq < 4; ++gq) {
+                float v[16], u[16];
+                tmem_ld16(tlane + TM_G + 16 * gq, v);
+                tmem_ld16(tlane + TM_G + 96 + 16 * gq, u);
+                if (lo_rows) {
+#pragma unroll
+                    for (int i = 0; i < 16; ++i) scr[m * SW + 16 * gq + i] = v[i] + u[i];
+                }
+            }
+            float v[16], f[16];
+            tmem_ld16(tlane + TM_G + 64, v);
+            tmem_ld16(tlane + TM_F, f);
             if (lo_rows) {
+                scr[m * SW + 64] = v[0];
 #pragma unroll
-                for (int i = 0; i < 16; ++i) scr[m * SW + 16 * gq + i] = v[i] + u[i];
+                for (int i = 0; i < 8; ++i) scr[m * SW + 72 + i] = f[i] + f[8 + i];
             }
         }
-        float v[16], f[16];
-        tmem_ld16(tlane + TM_G + 64, v);
-        tmem_ld16(tlane + TM_F, f);
-        if (lo_rows) {
-            scr[m * SW + 64] = v[0];
+        __syncthreads();
+        if (tid < 64) {
 #pragma unroll
-            for (int i = 0; i < 8; ++i) scr[m * SW + 72 + i] = f[i] + f[8 + i];
-        }
-    }
-    __syncthreads();
-    if (tid < 64) {
+            for (int gq = 0; gq < 4; ++gq) {
+                float v[16], u[16];
+                tmem_ld16(tlane + TM_G + 16 * gq, v);
+                tmem_ld16(tlane + TM_G + 96 + 16 * gq, u);
 #pragma unroll
-        for (int gq = 0; gq < 4; ++gq) {
-            float v[16], u[16];
-            tmem_ld16(tlane + TM_G + 16 * gq, v);
-            tmem_ld16(tlane + TM_G + 96 + 16 * gq, u);
-#pragma unroll
-            for (int i = 0; i < 16; ++i) scr[tid * SW + 16 * gq + i] += v[i] + u[i];
-        }
-        float v[16], f[16];
-        tmem_ld16(tlane + TM_G + 64, v);
-        tmem_ld16(tlane + TM_F, f);
-        scr[tid * SW + 64] += v[0];
-#pragma unroll
-        for (int i = 0; i < 8; ++i) scr[tid * SW + 72 + i] += f[i] + f[8 + i];
-    }
-    __syncthreads();
-    for (int e = tid; e < H * H; e += NT) out[L.off_w2() + e] = scr[(e >> 6) * SW + (e & 63)];
-    if (tid < H) {
-        out[L.off_b2() + tid] = scr[tid * SW + 64];  // G[:, 64]  (ones column)
-        out[L.off_b1() + tid] = scr[tid * SW + 72];  // F[:, 0]
-    }
-    for (int e = tid; e < H * O; e += NT) out[L.off_w1() + e] = scr[(e / O) * SW + 73 + (e % O)];
-    __syncthreads();
-    // dW3: sum the register accumulators over the 8 row groups of the warp, then over the 4 row quadrants
-    {
-#pragma unroll
-        for (int q = 0; q < A; ++q)
-#pragma unroll
-            for (int c = 0; c < 8; ++c) {
-                float v = gW3[q][c];
-                v += __shfl_xor_sync(0xffffffffu, v, 4);
-                v += __shfl_xor_sync(0xffffffffu, v, 8);
-                v += __shfl_xor_sync(0xffffffffu, v, 16);
-                if (g == 0) scr[(q4 * A + q) * H + c0 + 8 * (c >> 1) + 2 * p + (c & 1)] = v;
+                for (int i = 0; i < 16; ++i) scr[tid * SW + 16 * gq + i] += v[i] + u[i];
             }
-        __syncthreads();
-        for (int col = tid; col < A * H; col += NT)
-            out[L.off_w3() + col] = (scr[col] + scr[A * H + col]) + (scr[2 * A * H + col] + scr[3 * A * H + col]);
-        __syncthreads();
-    }
-    // row-owned scalars: every row's loss was computed by 4 threads; count one of them
-    {
-        constexpr int NS = A + 1 + 5;
-        float vals[NS];
-        const float keep = (hf == 0 && p < 2) ? 1.0f : 0.0f;
+            float v[16], f[16];
+            tmem_ld16(tlane + TM_G + 64, v);
+            tmem_ld16(tlane + TM_F, f);
+            scr[tid * SW + 64] += v[0];
 #pragma unroll
-        for (int q = 0; q < A; ++q) vals[q] = gB3[q] * keep;
-        vals[A] = racc.gLs * keep; vals[A + 1] = racc.st_loss * keep; vals[A + 2] = racc.st_kl * keep;
-        vals[A + 3] = racc.st_ent * keep; vals[A + 4] = racc.st_clip * keep; vals[A + 5] = racc.st_rows * keep;
-#pragma unroll
-        for (int s = 0; s < NS; ++s) {
-            float v = vals[s];
-#pragma unroll
-            for (int o = 16; o > 0; o >>= 1) v += __shfl_down_sync(0xffffffffu, v, o);
-            if (l == 0) scr[s * 8 + w] = v;
+            for (int i = 0; i < 8; ++i) scr[tid * SW + 72 + i] += f[i] + f[8 + i];
         }
         __syncthreads();
-        if (tid < NS) {
-            const float sum = (scr[tid * 8] + scr[tid * 8 + 1]) + (scr[tid * 8 + 2] + scr[tid * 8 + 3]);
-            if (tid < A) out[L.off_b3() + tid] = sum;
-            else if (tid == A) out[L.off_logstd()] = sum;
-            else out[P + (tid - A - 1)] = sum;
+        for (int e = tid; e < H * H; e += NT) out[L.off_w2() + e] = scr[(e >> 6) * SW + (e & 63)];
+        if (tid < H) {
+            out[L.off_b2() + tid] = scr[tid * SW + 64];  // G[:, 64]  (ones column)
+            out[L.off_b1() + tid] = scr[tid * SW + 72];  // F[:, 0]
         }
-        if (tid >= NS && tid < NS + (MLP_NSTATS - 5)) out[P + 5 + (tid - NS)] = 0.0f;
+        for (int e = tid; e < H * O; e += NT) out[L.off_w1() + e] = scr[(e / O) * SW + 73 + (e % O)];
+        __syncthreads();
+        // dW3: sum the register accumulators over the 8 row groups of the warp, then over the 4 row quadrants
+        {
+#pragma unroll
+            for (int q = 0; q < A; ++q)
+#pragma unroll
+                for (int c = 0; c < 8; ++c) {
+                    float v = gW3[q][c];
+                    v += __shfl_xor_sync(0xffffffffu, v, 4);
+                    v += __shfl_xor_sync(0xffffffffu, v, 8);
+                    v += __shfl_xor_sync(0xffffffffu, v, 16);
+                    if (g == 0) scr[(q4 * A + q) * H + c0 + 8 * (c >> 1) + 2 * p + (c & 1)] = v;
+                }
+            __syncthreads();
+            for (int col = tid; col < A * H; col += NT)
+                out[L.off_w3() + col] = (scr[col] + scr[A * H + col]) + (scr[2 * A * H + col] + scr[3 * A * H + col]);
+            __syncthreads();
+        }
+        // row-owned scalars: every row's loss was computed by 4 threads; count one of them
+        {
+            constexpr int NS = A + 1 + 5;
+            float vals[NS];
+            const float keep = (hf == 0 && p < 2) ? 1.0f : 0.0f;
+#pragma unroll
+            for (int q = 0; q < A; ++q) vals[q] = gB3[q] * keep;
+            vals[A] = racc.gLs * keep; vals[A + 1] = racc.st_loss * keep; vals[A + 2] = racc.st_kl * keep;
+            vals[A + 3] = racc.st_ent * keep; vals[A + 4] = racc.st_clip * keep; vals[A + 5] = racc.st_rows * keep;
+#pragma unroll
+            for (int s = 0; s < NS; ++s) {
+                float v = vals[s];
+#pragma unroll
+                for (int o = 16; o > 0; o >>= 1) v += __shfl_down_sync(0xffffffffu, v, o);
+                if (l == 0) scr[s * 8 + w] = v;
+            }
+            __syncthreads();
+            if (tid < NS) {
+                const float sum = (scr[tid * 8] + scr[tid * 8 + 1]) + (scr[tid * 8 + 2] + scr[tid * 8 + 3]);
+                if (tid < A) out[L.off_b3() + tid] = sum;
+                else if (tid == A) out[L.off_logstd()] = sum;
+                else if (with_stats) out[P + (tid - A - 1)] = sum;
+            }
+            if (with_stats && tid >= NS && tid < NS + (MLP_NSTATS - 5)) out[P + 5 + (tid - NS)] = 0.0f;
+            __syncthreads();
+        }
+        first = true;
+        zero_acc();
+        stamp(30);
     }
-    TC_STAMP(30);
-    tc_before_sync();
-    __syncthreads();
-    if (w == 1) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, 256;" ::"r"(tmem) : "memory");
+};
+
+template <int O, int A>
+__global__ void __maxnreg__(120) mlp_train_tc_kernel(const MlpArgs a) {
+    extern __shared__ __align__(1024) uint8_t smem[];
+    const MlpLayout L{O, H, A};
+    Cta<O, A> cta;
+    cta.init(smem);
+    cta.stamps = a.timing ? a.timing + (int64_t)blockIdx.x * 32 : nullptr;
+    cta.stamp(0);
+    if (a.step_counter && blockIdx.x == 0 && threadIdx.x == 0) *a.step_counter += 1ull;
+    cta.load_weights(a, a.params, [](const float* q) { return __ldg(q); });
+    cta.zero_acc();
+    cta.stamp(1);
+    cta.run_tiles(a, blockIdx.x, gridDim.x);
+    cta.write_partial(a.partial + (int64_t)blockIdx.x * (L.total() + MLP_NSTATS), true);
+    cta.fini();
 }
 }  // namespace tc

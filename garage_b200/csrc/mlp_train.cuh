@@ -44,6 +44,10 @@ struct MlpArgs {
     float* mean_out;        // [mb,A] or NULL (forward output, minibatch order)
     unsigned long long* step_counter;  // Adam step, ticked once per backward launch (or NULL)
     long long* timing;      // debug: [grid][32] clock64 stamps of the tensor-core kernel (or NULL)
+    // on-the-fly minibatch shuffle (tensor-core paths): row id = perm(start + m) over [0, perm_n)
+    int64_t perm_n;         // 0: off
+    int perm_half_bits;
+    uint32_t perm_keys[8];
 };
 
 

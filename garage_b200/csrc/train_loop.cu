@@ -1,0 +1,271 @@
+// Persistent training loop: ALL minibatch steps of `_train` (torch/algos/vpg.py:230-293 --
+// `for epoch: for minibatch: zero_grad; loss; backward; optimizer.step()` for the policy and
+// for the value function) in ONE cooperative launch.
+//
+// Grid = 2 CTAs per SM.  With two networks, CTAs [0, n) train the policy and CTAs [n, 2n) the
+// value function (one CTA of each per SM: while one waits for its MMAs the other runs its
+// CUDA-core stage); the two loops are independent, as in the reference, and never synchronise
+// with each other.  Per minibatch step every CTA of a network
+//   1. runs its 64-row tiles through the tcgen05 forward/loss/backward (mlp_tc.cuh) and writes
+//      its partial gradient vector,
+//   2. meets the other CTAs of the network at a device-wide barrier (atomic counter),
+//   3. reduces its slice of the parameters over all partials in a fixed order, applies
+//      torch.optim.Adam's update (same arithmetic as reduce_adam_kernel, mlp.cu) and
+//   4. after a second barrier reloads the updated parameters (W2 re-split into tf32 panels).
+// The minibatch shuffle is evaluated on the fly (b2g_perm_apply) or read from the supplied
+// index lists; weights, Adam moments and the step counter are updated in place.
+#include "mlp_tc.cuh"
+
+struct NetLoop {
+    MlpArgs a;  // data pointers + loss configuration (params/idx/start/mb/partial are set per step)
+    float* params;
+    float* adam_m;
+    float* adam_v;
+    unsigned long long* step;
+    double lr, beta1, beta2, eps;
+    int64_t B, mbs;
+    int epochs, shuffle;  // shuffle: 0 sequential, 1 device permutation, 2 index lists [epochs][B]
+    const int32_t* idx_all;
+    uint32_t seed_lo, seed_hi;
+    float* partial;       // [ctas][P + MLP_NSTATS]
+    unsigned int* sync;   // barrier counter, zero at launch
+};
+struct LoopArgs {
+    NetLoop net[2];
+    int n_nets, ctas_per_net;
+};
+
+__device__ __forceinline__ void net_barrier(unsigned int* ctr, unsigned int target) {
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        __threadfence();
+        atomicAdd(ctr, 1u);
+        unsigned int v;
+        unsigned int spin = 0;
+        do {
+            asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(ctr) : "memory");
+            if (++spin > (1u << 22)) __trap();  // a lost CTA must surface as an error, not as a hung GPU
+        } while (v < target);
+        __threadfence();
+    }
+    __syncthreads();
+}
+
+template <int O, int A>
+__device__ __forceinline__ void net_loop(const NetLoop& n, int j, int ctas, uint8_t* smem) {
+    using namespace tc;
+    const MlpLayout L{O, H, A};
+    const int P = L.total(), W = P + MLP_NSTATS;
+    Cta<O, A> cta;
+    cta.init(smem);
+    const int tid = threadIdx.x;
+    MlpArgs a = n.a;
+    a.params = n.params;
+    a.step_counter = nullptr;
+    a.timing = nullptr;
+    auto ld = [](const float* q) { return __ldcg(q); };  // parameters are rewritten by other CTAs: L2 only
+    unsigned long long t = *reinterpret_cast<volatile unsigned long long*>(n.step);
+    unsigned int nbar = 0;
+    const int ppc = (P + ctas - 1) / ctas;  // parameters reduced + updated by each CTA (<= 32)
+    float* scr = reinterpret_cast<float*>(smem + OFF_ACT);
+    float* out = n.partial + (int64_t)j * W;
+    cta.zero_acc();
+    cta.load_weights(a, n.params, ld);
+    const int64_t steps = (n.B + n.mbs - 1) / n.mbs;
+    for (int e = 0; e < n.epochs; ++e) {
+        a.perm_n = 0;
+        if (n.shuffle == 1) {  // the permutation b2g_permutation(seed, counter = Adam step at epoch start) draws
+            a.perm_n = n.B;
+            a.perm_half_bits = b2g_perm_half_bits(n.B);
+            b2g_perm_keys(n.seed_lo, n.seed_hi, (uint64_t)t, a.perm_keys);
+        }
+        for (int64_t s = 0; s < steps; ++s) {
+            a.start = s * n.mbs;
+            a.mb = (n.B - a.start) < n.mbs ? (n.B - a.start) : n.mbs;
+            a.idx = (n.shuffle == 2) ? n.idx_all + (int64_t)e * n.B + a.start : nullptr;
+            ++t;
+            if (tid == 64) {  // Adam bias corrections of this step, off the critical path
+                const double bc1 = 1.0 - pow(n.beta1, (double)t), bc2 = 1.0 - pow(n.beta2, (double)t);
+                float* adam_c = reinterpret_cast<float*>(smem + OFF_SMALL) + Small<O, A>::END;
+                adam_c[0] = (float)(n.lr / bc1);
+                adam_c[1] = (float)sqrt(bc2);
+            }
+            cta.run_tiles(a, j, ctas);
+            cta.write_partial(out, false);
+            net_barrier(n.sync, ++nbar * (unsigned int)ctas);
+            // ---- fixed-order reduction of this CTA's parameter slice + Adam (reduce_adam_kernel's arithmetic)
+            {
+                const int px = tid & 31, sl = tid >> 5;
+                const int pidx = j * ppc + px;
+                const bool own = px < ppc && pidx < P;
+                float sum = 0.0f;
+                if (own) {
+#pragma unroll 4
+                    for (int b = sl; b < ctas; b += 8) sum += __ldcg(n.partial + (int64_t)b * W + pidx);
+                }
+                scr[sl * 32 + px] = sum;
+                __syncthreads();
+                if (sl == 0 && own) {
+                    float tot = 0.0f;
+#pragma unroll
+                    for (int k = 0; k < 8; ++k) tot += scr[k * 32 + px];
+                    const float* adam_c = reinterpret_cast<const float*>(smem + OFF_SMALL) + Small<O, A>::END;
+                    const float g = tot * (1.0f / (float)a.mb);
+                    const float step_size = adam_c[0], bc2_sqrt = adam_c[1];
+                    float mm = n.adam_m[pidx], vv = n.adam_v[pidx];
+                    mm = mm + (float)(1.0 - n.beta1) * (g - mm);                 // exp_avg.lerp_(grad, 1-beta1)
+                    vv = vv * (float)n.beta2 + ((float)(1.0 - n.beta2) * g) * g;  // mul_(beta2).addcmul_(g, g, 1-beta2)
+                    const float denom = sqrtf(vv) / bc2_sqrt + (float)n.eps;
+                    n.params[pidx] = __ldcg(n.params + pidx) - step_size * (mm / denom);
+                    n.adam_m[pidx] = mm;
+                    n.adam_v[pidx] = vv;
+                }
+            }
+            net_barrier(n.sync, ++nbar * (unsigned int)ctas);
+            cta.load_weights(a, n.params, ld);
+        }
+    }
+    if (j == 0 && tid == 0) *n.step = t;
+    cta.fini();
+}
+
+template <int O, int AP>
+__global__ void __maxnreg__(120) train_loop_kernel(const __grid_constant__ LoopArgs args) {
+    extern __shared__ __align__(1024) uint8_t loop_smem_raw[];
+    uint8_t* smem = loop_smem_raw;
+    const int net = blockIdx.x / args.ctas_per_net, j = blockIdx.x % args.ctas_per_net;
+    if (net == 0 && args.net[0].a.loss_kind != LOSS_VF) net_loop<O, AP>(args.net[0], j, args.ctas_per_net, smem);
+    else net_loop<O, 1>(args.net[net], j, args.ctas_per_net, smem);
+}
+
+// ------------------------------------------------------------------ host --
+template <int O, int AP>
+static size_t loop_smem() {
+    const size_t a = tc::smem_bytes<O, AP>(), b = tc::smem_bytes<O, 1>();
+    return (a > b ? a : b) + 16;  // + Adam bias corrections
+}
+
+static int check_net(const b2g_train_net* t) {
+    B2G_CHECK_ARG(t->hidden == 64, "the fused training loop is built for hidden = (64, 64)");
+    B2G_CHECK_ARG(t->params && t->adam_m && t->adam_v && t->step_counter && t->obs, "NULL pointer");
+    B2G_CHECK_ARG(t->n_rows > 0 && t->epochs >= 0, "empty batch");
+    B2G_CHECK_ARG(t->loss_kind >= LOSS_PPO && t->loss_kind <= LOSS_VF, "bad loss_kind");
+    if (t->loss_kind == LOSS_VF) B2G_CHECK_ARG(t->ret && t->out_dim == 1, "value loss needs ret and out_dim 1");
+    else B2G_CHECK_ARG(t->act && t->adv && (t->loss_kind != LOSS_PPO || t->old_logp), "policy loss needs act, adv (and old_logp for PPO)");
+    B2G_CHECK_ARG(t->shuffle >= 0 && t->shuffle <= 2 && (t->shuffle != 2 || t->idx), "bad shuffle mode");
+    B2G_CHECK_ARG(t->n_rows <= 0x7fffffff, "n_rows out of range for int32 ids");
+    return B2G_OK;
+}
+
+static void fill_net(NetLoop& n, const b2g_train_net* t, int ctas, float* partial, unsigned int* sync) {
+    n = NetLoop{};
+    n.a.obs = t->obs; n.a.act = t->act; n.a.adv = t->adv; n.a.old_logp = t->old_logp; n.a.ret = t->ret;
+    n.a.loss_kind = t->loss_kind; n.a.flags = t->flags; n.a.clip = t->clip; n.a.ent_coeff = t->ent_coeff;
+    n.a.min_log_std = t->min_log_std; n.a.max_log_std = t->max_log_std;
+    n.params = t->params; n.adam_m = t->adam_m; n.adam_v = t->adam_v; n.step = t->step_counter;
+    n.lr = t->lr; n.beta1 = t->beta1; n.beta2 = t->beta2; n.eps = t->eps;
+    n.B = t->n_rows;
+    n.mbs = (t->minibatch > 0 && t->minibatch < t->n_rows) ? t->minibatch : t->n_rows;
+    n.epochs = t->epochs; n.shuffle = t->shuffle; n.idx_all = t->idx;
+    n.seed_lo = (uint32_t)t->shuffle_seed; n.seed_hi = (uint32_t)(t->shuffle_seed >> 32);
+    n.partial = partial; n.sync = sync;
+    (void)ctas;
+}
+
+extern "C" int64_t b2g_mlp_train_loop_ws_floats(void) {
+    // two networks x (2 SMs worth of CTAs) x (largest built parameter vector + statistics) + barrier counters
+    const int64_t P = MlpLayout{4, 64, 4}.total() + MLP_NSTATS;
+    return 2 * (int64_t)b2g_sm_count() * P + 64;
+}
+
+template <int O, int AP>
+static int launch_loop(const LoopArgs& args, int grid, cudaStream_t s) {
+    const size_t smem = loop_smem<O, AP>();
+    static bool configured = false;
+    if (!configured) {
+        B2G_CUDA(cudaFuncSetAttribute(train_loop_kernel<O, AP>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        B2G_CUDA(cudaFuncSetAttribute(train_loop_kernel<O, AP>, cudaFuncAttributePreferredSharedMemoryCarveout,
+                                      cudaSharedmemCarveoutMaxShared));
+        // The grid (2 CTAs per SM) must be co-resident: its CTAs wait for each other.  The runtime's
+        // occupancy calculator answers 1 for every kernel that allocates tensor memory (so a
+        // cooperative launch of this grid is refused), although two CTAs with 256 TMEM columns each
+        // do share an SM; check the two budgets that decide it here instead.
+        cudaFuncAttributes fa{};
+        B2G_CUDA(cudaFuncGetAttributes(&fa, train_loop_kernel<O, AP>));
+        int dev = 0, regs_sm = 0, smem_sm = 0;
+        B2G_CUDA(cudaGetDevice(&dev));
+        B2G_CUDA(cudaDeviceGetAttribute(&regs_sm, cudaDevAttrMaxRegistersPerMultiprocessor, dev));
+        B2G_CUDA(cudaDeviceGetAttribute(&smem_sm, cudaDevAttrMaxSharedMemoryPerMultiprocessor, dev));
+        const int regs_cta = ((fa.numRegs + 7) / 8 * 8) * tc::NT;
+        if (2 * regs_cta > regs_sm - 4096 || 2 * (smem + 1024 + 128) > (size_t)smem_sm) {
+            b2g_set_error("b2g_mlp_train_loop: two CTAs do not fit one SM (registers %d x 2 of %d, shared %zu x 2 of %d)",
+                          regs_cta, regs_sm, smem + 1024, smem_sm);
+            return B2G_ERR_UNSUPPORTED;
+        }
+        configured = true;
+    }
+    train_loop_kernel<O, AP><<<grid, tc::NT, smem, s>>>(args);
+    B2G_CHECK_LAUNCH();
+    return B2G_OK;
+}
+
+extern "C" int b2g_mlp_train_loop(const b2g_train_net* nets, int n_nets, float* workspace,
+                                  int64_t workspace_floats, void* stream) {
+    B2G_CHECK_ARG(nets && (n_nets == 1 || n_nets == 2), "one or two networks");
+    B2G_CHECK_ARG(workspace && workspace_floats >= b2g_mlp_train_loop_ws_floats(), "workspace too small");
+    for (int i = 0; i < n_nets; ++i) {
+        const int rc = check_net(&nets[i]);
+        if (rc != B2G_OK) return rc;
+    }
+    B2G_CHECK_ARG(n_nets == 1 || nets[0].obs_dim == nets[1].obs_dim, "both networks read the same observations");
+    B2G_CHECK_ARG(n_nets == 1 || nets[1].out_dim == 1, "the second network is the value function (out_dim 1)");
+    cudaStream_t s = (cudaStream_t)stream;
+    const int grid = 2 * b2g_sm_count();
+    LoopArgs args{};
+    args.n_nets = n_nets;
+    args.ctas_per_net = grid / n_nets;
+    unsigned int* sync = reinterpret_cast<unsigned int*>(workspace);
+    float* partial = workspace + 64;
+    B2G_CUDA(cudaMemsetAsync(sync, 0, 256, s));
+    int64_t off = 0;
+    for (int i = 0; i < n_nets; ++i) {
+        fill_net(args.net[i], &nets[i], args.ctas_per_net, partial + off, sync + 16 * i);
+        off += (int64_t)args.ctas_per_net *
+               (MlpLayout{nets[i].obs_dim, 64, nets[i].out_dim}.total() + MLP_NSTATS);
+    }
+    const int O = nets[0].obs_dim, AP = nets[0].out_dim;
+#define B2G_LOOP_CASE(OO, AA) \
+    if (O == OO && AP == AA) return launch_loop<OO, AA>(args, grid, s);
+    B2G_LOOP_CASE(3, 1) B2G_LOOP_CASE(3, 2) B2G_LOOP_CASE(4, 1)
+#undef B2G_LOOP_CASE
+    b2g_set_error("b2g_mlp_train_loop: obs=%d out=%d is not built (built: (3,1), (3,2), (4,1))", O, AP);
+    return B2G_ERR_UNSUPPORTED;
+}
+
+// debug: registers / occupancy of the tensor-core kernels as the driver sees them
+template <class K>
+static void print_occ(const char* name, K kernel, size_t smem) {
+    cudaFuncAttributes fa{};
+    cudaFuncGetAttributes(&fa, kernel);
+    cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    cudaFuncSetAttribute(kernel, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
+    int occ = 0, occ0 = 0;
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kernel, tc::NT, smem);
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ0, kernel, tc::NT, 0);
+    printf("%-28s regs %3d  maxThreads %4d  smem %zu  occupancy %d (without smem %d)\n", name, fa.numRegs,
+           fa.maxThreadsPerBlock, smem, occ, occ0);
+}
+extern "C" int b2g_debug_occupancy(void) {
+    print_occ("mlp_train_tc<3,1>", tc::mlp_train_tc_kernel<3, 1>, tc::smem_bytes<3, 1>());
+    print_occ("mlp_train_tc<3,2>", tc::mlp_train_tc_kernel<3, 2>, tc::smem_bytes<3, 2>());
+    print_occ("mlp_train_tc<4,1>", tc::mlp_train_tc_kernel<4, 1>, tc::smem_bytes<4, 1>());
+    print_occ("train_loop<3,1>", train_loop_kernel<3, 1>, loop_smem<3, 1>());
+    print_occ("train_loop<3,2>", train_loop_kernel<3, 2>, loop_smem<3, 2>());
+    print_occ("train_loop<4,1>", train_loop_kernel<4, 1>, loop_smem<4, 1>());
+    int dev = 0, regs = 0, smem_sm = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&regs, cudaDevAttrMaxRegistersPerMultiprocessor, dev);
+    cudaDeviceGetAttribute(&smem_sm, cudaDevAttrMaxSharedMemoryPerMultiprocessor, dev);
+    printf("device: %d registers / SM, %d B shared memory / SM\n", regs, smem_sm);
+    return B2G_OK;
+}

@@ -364,6 +364,61 @@ def mlp_reduce(shape, n_partials, scale, *, grad_out=None, stats_out=None, param
              float(beta1), float(beta2), float(eps), _stream(shape.ws))
 
 
+def mlp_path():
+    """0: tcgen05 for hidden 64 (default); 1: CUDA-core fp32 everywhere (B2G_MLP_PATH=ffma)."""
+    return int(_lib.load().b2g_get_mlp_path())
+
+
+def set_mlp_path(path):
+    _lib.check(_lib.load().b2g_set_mlp_path(int(path)), 'b2g_set_mlp_path')
+
+
+SHUFFLE_NONE, SHUFFLE_DEVICE, SHUFFLE_IDS = 0, 1, 2
+_loop_ws = {}
+
+
+def mlp_train_loop(nets):
+    """All minibatch steps of `_train` for one or two networks in one cooperative launch
+    (b2g_mlp_train_loop).  `nets`: dicts with shape, params, adam_m, adam_v, step_counter, lr,
+    beta1, beta2, eps, obs, [act, adv, old_logp | ret], loss_kind, flags, clip, ent_coeff,
+    min_log_std, max_log_std, minibatch (None = full batch), epochs, shuffle, shuffle_seed, idx."""
+    lib = _lib.load()
+    arr = (_lib.TrainNet * len(nets))()
+    dev = nets[0]['params'].device
+    for t, n in zip(arr, nets):
+        shape = n['shape']
+        for name in ('params', 'adam_m', 'adam_v', 'obs', 'act', 'adv', 'old_logp', 'ret'):
+            _chk(n.get(name), torch.float32, name)
+        _chk(n.get('idx'), torch.int32, 'idx')
+        _chk(n['step_counter'], torch.int64, 'step_counter')
+        if n['params'].numel() != shape.P:
+            raise ValueError('params has {} elements, expected {}'.format(n['params'].numel(), shape.P))
+        B = n['obs'].shape[0]
+        t.obs_dim, t.hidden, t.out_dim = shape.O, shape.H, shape.A
+        t.params, t.adam_m, t.adam_v = ptr(n['params']), ptr(n['adam_m']), ptr(n['adam_v'])
+        t.step_counter = ptr(n['step_counter'])
+        t.lr, t.beta1, t.beta2, t.eps = float(n['lr']), float(n['beta1']), float(n['beta2']), float(n['eps'])
+        t.obs, t.act, t.adv = ptr(n['obs']), ptr(n.get('act')), ptr(n.get('adv'))
+        t.old_logp, t.ret = ptr(n.get('old_logp')), ptr(n.get('ret'))
+        t.loss_kind, t.flags = int(n['loss_kind']), int(n.get('flags', 0))
+        t.clip, t.ent_coeff = float(n.get('clip', 0.2)), float(n.get('ent_coeff', 0.0))
+        t.min_log_std, t.max_log_std = float(n.get('min_log_std', -INF)), float(n.get('max_log_std', INF))
+        t.n_rows = B
+        t.minibatch = int(n['minibatch']) if n.get('minibatch') else 0
+        t.epochs, t.shuffle = int(n['epochs']), int(n.get('shuffle', SHUFFLE_NONE))
+        t.shuffle_seed = int(n.get('shuffle_seed', 0)) & (2**64 - 1)
+        idx = n.get('idx')
+        if idx is not None and idx.numel() != t.epochs * B:
+            raise ValueError('idx must hold epochs x n_rows ids')
+        t.idx = ptr(idx)
+    need = int(lib.b2g_mlp_train_loop_ws_floats())
+    ws = _loop_ws.get(dev)
+    if ws is None or ws.numel() < need:
+        ws = _loop_ws[dev] = torch.empty(need, dtype=torch.float32, device=dev)
+    with torch.cuda.device(dev):
+        call('b2g_mlp_train_loop', arr, len(nets), ptr(ws), ws.numel(), _stream(ws))
+
+
 def adam_step(params, grad, grad_scale, adam_m, adam_v, step_counter, lr, beta1=0.9, beta2=0.999,
               eps=1e-8):
     with torch.cuda.device(params.device):

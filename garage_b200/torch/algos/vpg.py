@@ -46,6 +46,10 @@ class VPG(RLAlgorithm):
             zero-padded observations leak V(0) into early-terminated episodes).
         process_group: torch.distributed group for the gradient all-reduce (default: the
             world group when torch.distributed is initialised with world_size > 1).
+        update_mode (str): 'fused' runs every minibatch step of `_train` (both networks) in one
+            persistent cooperative launch (b2g_mlp_train_loop; hidden sizes (64, 64), one rank);
+            'stepwise' launches one gradient + one Adam kernel per minibatch step; 'auto'
+            (default) picks 'fused' whenever it applies.
     """
     _loss_kind = ops.LOSS_VPG
     _clip = 0.0
@@ -55,7 +59,7 @@ class VPG(RLAlgorithm):
                  center_adv=True, positive_adv=False, policy_ent_coeff=0.0,
                  use_softplus_entropy=False, stop_entropy_gradient=False,
                  entropy_method='no_entropy', *, shuffle='device', pad_value_mode='mask',
-                 shuffle_seed=0, process_group=None, log_stats=True):
+                 shuffle_seed=0, process_group=None, log_stats=True, update_mode='auto'):
         self._discount = discount
         self.policy = policy
         self.max_episode_length = env_spec.max_episode_length
@@ -86,6 +90,9 @@ class VPG(RLAlgorithm):
         self._pad_value_mode = pad_value_mode
         self._pg = process_group
         self._log_stats = log_stats
+        if update_mode not in ('auto', 'fused', 'stepwise'):
+            raise ValueError("update_mode must be 'auto', 'fused' or 'stepwise'")
+        self._update_mode = update_mode
         self.last_stats = {}
 
     @staticmethod
@@ -314,8 +321,48 @@ class VPG(RLAlgorithm):
             if host_ids is not None:
                 np.random.shuffle(host_ids)
 
+    def _fused_applies(self):
+        if self._update_mode == 'stepwise' or self._world() > 1:
+            return False
+        ok = (self.policy.mlp_shape.H == 64 and self._value_function.mlp_shape.H == 64 and
+              ops.mlp_path() == 0)
+        if not ok and self._update_mode == 'fused':
+            raise NotImplementedError("update_mode='fused' needs hidden sizes (64, 64) and the tcgen05 path")
+        return ok
+
+    def _loop_net(self, opt, module_owner, f, policy):
+        """One network of the fused loop; draws the reference's BatchDataset shuffles here
+        (numpy's global RNG, in the reference's order) when shuffle='numpy'."""
+        m, v, step = opt.state()
+        B, E = f.B, opt.max_optimization_epochs
+        net = dict(shape=module_owner.mlp_shape, params=module_owner.flat, adam_m=m, adam_v=v,
+                   step_counter=step, lr=opt.lr, beta1=opt.beta1, beta2=opt.beta2, eps=opt.eps,
+                   obs=f.obs, minibatch=opt.minibatch_size, epochs=E)
+        if policy:
+            net.update(act=f.act, adv=f.adv, old_logp=f.old_logp, **self._policy_kwargs())
+        else:
+            net.update(ret=f.ret, loss_kind=ops.LOSS_VF)
+        if opt.minibatch_size is None:
+            net['shuffle'] = ops.SHUFFLE_NONE
+        elif self._shuffle == 'numpy':
+            ids = np.empty((E, B), dtype=np.int32)
+            host_ids = np.arange(B)
+            np.random.shuffle(host_ids)  # BatchDataset.__init__ (minibatch_dataset.py:14-24)
+            for e in range(E):
+                ids[e] = host_ids
+                np.random.shuffle(host_ids)  # after every epoch, the last included (:35)
+            net.update(shuffle=ops.SHUFFLE_IDS, idx=torch.from_numpy(ids).to(f.obs.device))
+        else:
+            net.update(shuffle=ops.SHUFFLE_DEVICE, shuffle_seed=self._shuffle_seed)
+        return net
+
     def _train(self, f):
-        """vpg.py:230-248: all policy minibatches, then all value-function minibatches."""
+        """vpg.py:230-248: all policy minibatches, then all value-function minibatches (the two
+        loops touch disjoint state, so the fused path runs them side by side)."""
+        if self._fused_applies():
+            ops.mlp_train_loop([self._loop_net(self._policy_optimizer, self.policy, f, True),
+                                self._loop_net(self._vf_optimizer, self._value_function, f, False)])
+            return
         self._run_minibatches(self._policy_optimizer, self.policy, f, policy=True)
         self._run_minibatches(self._vf_optimizer, self._value_function, f, policy=False)
 

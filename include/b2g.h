@@ -261,6 +261,40 @@ int b2g_mlp_num_partials(int obs_dim, int hidden, int out_dim, int backward, int
  * variable B2G_MLP_PATH=ffma.  Both paths meet the 1e-5 parity bar of the same reference code. */
 int b2g_set_mlp_path(int path);
 int b2g_get_mlp_path(void);
+/* ---- fused training loop ------------------------------------------------------------------
+ * ALL minibatch steps of VPG/PPO._train (torch/algos/vpg.py:230-293: for epoch, for minibatch:
+ * optimizer.zero_grad(); loss; backward(); optimizer.step(), first for the policy, then for the
+ * value function) in one cooperative launch.  One b2g_train_net per network; with two networks
+ * the policy and value-function loops run concurrently on disjoint CTAs (they are independent
+ * in the reference as well).  Parameters, Adam moments and the step counter are updated in
+ * place.  shuffle: 0 = rows in order (minibatch = NULL/full batch), 1 = the permutation
+ * b2g_permutation(shuffle_seed, counter = step counter at the start of the epoch) would write,
+ * evaluated on the fly, 2 = `idx` holds [epochs][n_rows] int32 row ids (the reference's
+ * BatchDataset order).  hidden must be 64 (tcgen05 path); workspace holds at least
+ * b2g_mlp_train_loop_ws_floats() floats. */
+typedef struct b2g_train_net {
+    int obs_dim, hidden, out_dim;
+    float* params;                       /* flat parameter vector, updated in place */
+    float* adam_m;
+    float* adam_v;
+    unsigned long long* step_counter;    /* device u64: Adam step, advanced by epochs*ceil(n_rows/minibatch) */
+    double lr, beta1, beta2, eps;
+    const float* obs;                    /* [n_rows, obs_dim] */
+    const float* act;                    /* [n_rows, out_dim]  policy losses */
+    const float* adv;                    /* [n_rows] */
+    const float* old_logp;               /* [n_rows]           PPO */
+    const float* ret;                    /* [n_rows]           value loss */
+    int loss_kind, flags;                /* as b2g_mlp_minibatch_grad */
+    float clip, ent_coeff, min_log_std, max_log_std;
+    int64_t n_rows, minibatch;           /* minibatch <= 0: full batch */
+    int epochs, shuffle;
+    uint64_t shuffle_seed;
+    const int32_t* idx;
+} b2g_train_net;
+int64_t b2g_mlp_train_loop_ws_floats(void);
+int b2g_mlp_train_loop(const b2g_train_net* nets, int n_nets, float* workspace,
+                       int64_t workspace_floats, void* stream);
+
 /* Debug only: device buffer [grid][32] of int64 that the tcgen05 kernel fills with clock64()
  * stamps of its stages (NULL switches it off, the default). */
 int b2g_mlp_debug_timing(long long* buf);

@@ -1,0 +1,97 @@
+"""GPU parity of the fused training loop (b2g_mlp_train_loop: every minibatch step of
+`_train`, both networks, one cooperative launch) against the step-wise path
+(b2g_mlp_minibatch_grad + b2g_mlp_reduce per minibatch), which the other GPU tests pin to the
+oracle and to the reference's golden fixtures.  Same data, same shuffles, same Adam state:
+the parameters after all steps must agree within 1e-5 relative (fp32)."""
+import numpy as np
+import pytest
+import torch
+
+from tests.test_e2e_gpu import build
+
+pytestmark = pytest.mark.gpu
+
+
+def _rel(a, b):
+    a, b = a.double(), b.double()
+    return float((a - b).norm() / b.norm().clamp_min(1e-30))
+
+
+def _run(env_cls, algo, mode, n_envs, epochs, mb, seed_np=None, hidden=(64, 64), **kw):
+    env = env_cls(max_episode_length=40)
+    a, policy, vf, sampler = build(env, hidden=hidden, n_envs=n_envs, algo=algo, epochs=epochs, mb=mb,
+                                   update_mode=mode, **kw)
+    if seed_np is not None:
+        np.random.seed(seed_np)
+    for itr in range(2):
+        eps = sampler.obtain_samples(itr, n_envs * 40, policy)
+        a._train_once(itr, eps)
+    torch.cuda.synchronize()
+    steps = [int(o.state()[2].item()) for o in (a._policy_optimizer, a._vf_optimizer)]
+    return policy.flat.clone(), vf.flat.clone(), steps, dict(a.last_stats)
+
+
+@pytest.mark.parametrize('algo', ['ppo', 'vpg'])
+@pytest.mark.parametrize('mb', [None, 512, 1000])
+def test_fused_matches_stepwise_device_shuffle(algo, mb):
+    from garage_b200.envs import PendulumEnv
+    pf, vf_, sf, lf = _run(PendulumEnv, algo, 'fused', 64, 3, mb)
+    ps, vs, ss, ls = _run(PendulumEnv, algo, 'stepwise', 64, 3, mb)
+    assert sf == ss and sf[0] == 2 * 3 * (1 if mb is None else -(-2560 // mb))
+    assert _rel(pf, ps) < 1e-5 and _rel(vf_, vs) < 1e-5
+    for k in ('GaussianMLPPolicy/LossAfter', 'GaussianMLPPolicy/KL', 'GaussianMLPValueFunction/LossAfter'):
+        assert abs(lf[k] - ls[k]) <= 1e-5 * max(1.0, abs(ls[k])) + 1e-7, k
+
+
+def test_fused_matches_stepwise_numpy_shuffle_cartpole():
+    """shuffle='numpy' (the reference's BatchDataset order) and ragged episodes (CartPole
+    terminates early), obs_dim 4."""
+    from garage_b200.envs import CartPoleEnv
+    pf, vf_, sf, _ = _run(CartPoleEnv, 'ppo', 'fused', 128, 2, 700, seed_np=5, shuffle='numpy')
+    ps, vs, ss, _ = _run(CartPoleEnv, 'ppo', 'stepwise', 128, 2, 700, seed_np=5, shuffle='numpy')
+    assert sf == ss
+    assert _rel(pf, ps) < 1e-5 and _rel(vf_, vs) < 1e-5
+
+
+def test_fused_two_action_dims_pointenv():
+    from garage_b200.envs import PointEnv
+    pf, vf_, sf, _ = _run(PointEnv, 'ppo', 'fused', 64, 2, 640)
+    ps, vs, ss, _ = _run(PointEnv, 'ppo', 'stepwise', 64, 2, 640)
+    assert sf == ss
+    assert _rel(pf, ps) < 1e-5 and _rel(vf_, vs) < 1e-5
+
+
+def test_fused_refuses_other_hidden_sizes():
+    from garage_b200.envs import PendulumEnv
+    env = PendulumEnv(max_episode_length=40)
+    a, policy, vf, sampler = build(env, hidden=(32, 32), n_envs=16, update_mode='fused')
+    eps = sampler.obtain_samples(0, 16 * 40, policy)
+    with pytest.raises(NotImplementedError):
+        a._train_once(0, eps)
+
+
+def test_fused_matches_oracle_adam_sequence():
+    """Three full-batch value-function steps through the fused loop vs the float64 oracle
+    (forward, Gaussian NLL, backward, Adam) on the same data."""
+    from garage_b200 import ops
+    from oracle import np_oracle as O
+    rng = np.random.default_rng(3)
+    dev = torch.device('cuda:0')
+    Od, H, A, n = 3, 64, 1, 777
+    shape = ops.MlpShape(Od, H, A, dev)
+    flat = (rng.standard_normal(shape.P) * 0.5 / np.sqrt(H)).astype(np.float32)
+    obs = rng.standard_normal((n, Od)).astype(np.float32)
+    ret = (rng.standard_normal(n) * 3).astype(np.float32)
+    t = lambda x: torch.from_numpy(x).to(dev)
+    params, m, v = t(flat.copy()), torch.zeros(shape.P, device=dev), torch.zeros(shape.P, device=dev)
+    step = torch.zeros(1, dtype=torch.int64, device=dev)
+    ops.mlp_train_loop([dict(shape=shape, params=params, adam_m=m, adam_v=v, step_counter=step, lr=2.5e-4,
+                             beta1=0.9, beta2=0.999, eps=1e-8, obs=t(obs), ret=t(ret), loss_kind=ops.LOSS_VF,
+                             minibatch=None, epochs=3)])
+    torch.cuda.synchronize()
+    assert int(step.item()) == 3
+    o_p, o_m, o_v = flat.copy(), np.zeros_like(flat), np.zeros_like(flat)
+    for it in range(1, 4):
+        _, g = O.vf_loss_and_grad(o_p, Od, H, obs, ret)
+        o_p, o_m, o_v = O.adam_step(o_p, g.astype(np.float32), o_m, o_v, it, lr=2.5e-4)
+    assert np.allclose(params.cpu().numpy(), o_p, rtol=1e-5, atol=1e-6)
