@@ -72,6 +72,7 @@ SIGNATURES = {
     'b2g_adam_step': (c_int, [P, P, c_float, P, P, P, c_double, c_double, c_double, c_double,
                               c_int, P]),
     'b2g_mlp_train_loop_ws_floats': (c_int64, []),
+    'b2g_mlp_train_loop_debug_timing': (c_int, [P, c_int]),
     'b2g_mlp_train_loop': (c_int, [POINTER(TrainNet), c_int, P, c_int64, P]),
 }
 

@@ -124,6 +124,22 @@ __device__ __forceinline__ void tmem_ld16(uint32_t taddr, float (&v)[16]) {
     for (int i = 0; i < 16; ++i) v[i] = __uint_as_float(u[i]);
 }
 
+__device__ __forceinline__ void tmem_ld16_nowait(uint32_t taddr, float (&v)[16]) {
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x16.b32 "
+        "{%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15}, [%16];"
+        : "=f"(v[0]), "=f"(v[1]), "=f"(v[2]), "=f"(v[3]), "=f"(v[4]), "=f"(v[5]), "=f"(v[6]), "=f"(v[7]),
+          "=f"(v[8]), "=f"(v[9]), "=f"(v[10]), "=f"(v[11]), "=f"(v[12]), "=f"(v[13]), "=f"(v[14]), "=f"(v[15])
+        : "r"(taddr)
+        : "memory");
+}
+__device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
+// pins the uses of registers filled by tmem_ld16_nowait behind the wait (volatile asms keep their order)
+__device__ __forceinline__ void tmem_ld_use(float (&v)[16]) {
+    asm volatile("" : "+f"(v[0]), "+f"(v[1]), "+f"(v[2]), "+f"(v[3]), "+f"(v[4]), "+f"(v[5]), "+f"(v[6]), "+f"(v[7]),
+                      "+f"(v[8]), "+f"(v[9]), "+f"(v[10]), "+f"(v[11]), "+f"(v[12]), "+f"(v[13]), "+f"(v[14]), "+f"(v[15]));
+}
+
 // tanh x = 1 - 2 / (1 + e^{2x}) with the SFU's ex2 / rcp: absolute error ~2e-7 (|tanh| <= 1),
 // a quarter of tanhf's instruction count; saturates correctly (e -> inf: 1, e -> 0: -1)
 __device__ __forceinline__ float tanh_sfu(float x) {
@@ -216,7 +232,8 @@ struct Small {  // float offsets inside the small region
     static constexpr int NIN = A + 3;  // act[A], adv, old_logp, ret
     static constexpr int W1 = 0, B1 = W1 + H * O, B2 = B1 + H, W3 = B2 + H, B3 = W3 + A * H,
                          X = B3 + 4, MU = X + R * 4, IN = MU + 2 * A * R, SRC = IN + R * NIN + (R * NIN) % 2,
-                         BARS = SRC + 2 * R /* int64[R] */, TSLOT = BARS + 8 /* 4 x u64 */, END = TSLOT + 4;
+                         NEXT = SRC + 2 * R /* int64[R] */, BARS = NEXT + 4 * R /* int64[2][R] */,
+                         TSLOT = BARS + 8 /* 4 x u64 */, END = TSLOT + 4;
 };
 template <int O, int A>
 constexpr size_t smem_bytes() { return OFF_SMALL + sizeof(float) * Small<O, A>::END; }
@@ -266,7 +283,7 @@ struct Cta {
     static constexpr int NIN = S::NIN;
     uint8_t* smem;
     float *sm, *sW1, *sB1, *sB2, *sW3, *sB3, *sX, *sMu, *sIn;
-    int64_t* sSrc;
+    int64_t *sSrc, *sNext;
     uint32_t sb, bar1, bar2, bar3, bar4, tmem, tiles_done;
     int tid, w, l, q4, hf, g, p, ra, rb, c0;
     bool first;  // no MMA has written the G/F accumulators since the last readout
@@ -274,6 +291,8 @@ struct Cta {
     float gW3[A][8], gB3[A];
     MlpRowAcc racc;
     long long* stamps;
+    int64_t src_n;          // gather pipeline: row id / data of this thread's row in the next tile
+    RowData<O, A> row_n;
 
     __device__ __forceinline__ void stamp(int i) const {
         if (stamps && tid == 0 && i < 32) stamps[i] = clock64();
@@ -286,6 +305,7 @@ struct Cta {
         sW1 = sm + S::W1; sB1 = sm + S::B1; sB2 = sm + S::B2; sW3 = sm + S::W3; sB3 = sm + S::B3;
         sX = sm + S::X; sMu = sm + S::MU; sIn = sm + S::IN;
         sSrc = reinterpret_cast<int64_t*>(sm + S::SRC);
+        sNext = reinterpret_cast<int64_t*>(sm + S::NEXT);
         uint32_t* tslot = reinterpret_cast<uint32_t*>(sm + S::TSLOT);
         sb = smem_u32(smem);
         bar1 = smem_u32(sm + S::BARS); bar2 = bar1 + 8; bar3 = bar1 + 16; bar4 = bar1 + 24;
@@ -362,6 +382,23 @@ struct Cta {
         racc = MlpRowAcc{};
     }
 
+    // Gather pipeline: threads 0..R-1 own one row and load its data one tile ahead; threads
+    // R..2R-1 evaluate the row ids (index list or on-the-fly permutation) two tiles ahead while
+    // the CTA waits for GEMM1, and hand them over in shared memory (sNext, double-buffered), so
+    // no stage waits on a dependent load or on the permutation arithmetic.  prime() starts the
+    // pipeline for run_tiles(a, tile0, stride); neither ids nor row data depend on the weights,
+    // so the training loop primes the next minibatch before it waits for the other CTAs.
+    __device__ __forceinline__ void prime(const MlpArgs& a, int64_t tile0, int64_t stride) {
+        const int64_t ntiles = (a.mb + R - 1) / R;
+        src_n = -1;
+        if (tid < R) {
+            src_n = tile0 < ntiles ? mb_src(a, tile0 * R + tid) : -1;
+            row_n = load_row<O, A>(a, src_n);
+        } else if (tid < 2 * R) {
+            sNext[tid - R] = tile0 + stride < ntiles ? mb_src(a, (tile0 + stride) * R + (tid - R)) : -1;
+        }
+    }
+
     // forward + loss + backward of the 64-row tiles tile0, tile0 + stride, ... of minibatch `a`;
     // gradients accumulate in TMEM (G, F) and registers until write_partial()
     __device__ __forceinline__ void run_tiles(const MlpArgs& a, int64_t tile0, int64_t stride) {
@@ -381,15 +418,6 @@ struct Cta {
 #pragma unroll
                 for (int q = 0; q < A; ++q) w3c[q][2 * i + e] = sW3[q * H + c];
             }
-        // gather pipeline (threads 0..R-1 own one row): row ids run two tiles ahead of the tile
-        // being computed, row data one tile ahead, so no stage waits on a dependent load
-        int64_t src_n = -1, src_nn = -1;
-        RowData<O, A> row_n;
-        if (tid < R) {
-            src_n = tile0 < ntiles ? mb_src(a, tile0 * R + tid) : -1;
-            src_nn = tile0 + stride < ntiles ? mb_src(a, (tile0 + stride) * R + tid) : -1;
-            row_n = load_row<O, A>(a, src_n);
-        }
         int it = 0;
         for (int64_t tile = tile0; tile < ntiles; tile += stride, ++it) {
             const uint32_t par = tiles_done & 1;
@@ -416,12 +444,12 @@ struct Cta {
                 *reinterpret_cast<float4*>(aug + o0 + 16) = make_float4(xh[4], xh[5], xh[6], xh[7]);
                 *reinterpret_cast<float4*>(aug + o1) = make_float4(xl[0], xl[1], xl[2], xl[3]);
                 *reinterpret_cast<float4*>(aug + o1 + 16) = make_float4(xl[4], xl[5], xl[6], xl[7]);
-                src_n = src_nn;
-                row_n = load_row<O, A>(a, src_n);
-                const int64_t t2 = tile + 2 * stride;
-                src_nn = t2 < ntiles ? mb_src(a, t2 * R + tid) : -1;
             }
             __syncthreads();
+            if (tid < R) {  // next tile's rows (ids published during the previous tile / before the loop)
+                src_n = sNext[(it & 1) * R + tid];
+                row_n = load_row<O, A>(a, src_n);
+            }
             stamp(3 + 10 * it);
             // ---- L1: h1 = tanh(W1 x + b1); a quarter-warp writes the 8 chunks of one row (conflict-free)
             {
@@ -463,6 +491,10 @@ struct Cta {
                 __syncwarp();
             }
             stamp(5 + 10 * it);
+            if (tid >= R && tid < 2 * R) {  // row ids of the tile after next, off the critical path
+                const int64_t t2 = tile + 2 * stride;
+                sNext[((it + 1) & 1) * R + (tid - R)] = t2 < ntiles ? mb_src(a, t2 * R + (tid - R)) : -1;
+            }
             mbar_wait(bar1, par);
             tc_after_sync();
             stamp(6 + 10 * it);
@@ -622,75 +654,50 @@ struct Cta {
             __syncthreads();
             return;
         }
-        // every lane folds its own hi/lo column groups; lanes 64..127 (the lo-split rows) park the
-        // result in smem, lanes 0..63 add theirs, then every thread stores coalesced
+        // Stage 1: every lane of G/F folds its own hi/lo column groups into scr[lane][81]
+        // (lanes 64..127 hold the lo-split rows of dz); the register accumulators (dW3, row sums)
+        // are reduced with shuffles into scr2.  Stage 2 (after one barrier): all threads add the
+        // two lane halves / warp partials and store coalesced.
+        float* scr2 = scr + 128 * SW;  // [4][A*H] dW3 partials | [NS][8] row sums
+        constexpr int NS = A + 1 + 5;
+        float* scr3 = scr2 + 4 * A * H;
         if (tid < 128) {
-            const int m = tid & 63;
-            const bool lo_rows = tid >= 64;
 #pragma unroll
-            for (int gq = 0; gq < 4; ++gq) {
-                float v[16], u[16];
-                tmem_ld16(tlane + TM_G + 16 * gq, v);
-                tmem_ld16(tlane + TM_G + 96 + 16 * gq, u);
-                if (lo_rows) {
+            for (int gq = 0; gq < 4; gq += 2) {
+                float v0[16], u0[16], v1[16], u1[16];
+                tmem_ld16_nowait(tlane + TM_G + 16 * gq, v0);
+                tmem_ld16_nowait(tlane + TM_G + 96 + 16 * gq, u0);
+                tmem_ld16_nowait(tlane + TM_G + 16 * gq + 16, v1);
+                tmem_ld16_nowait(tlane + TM_G + 96 + 16 * gq + 16, u1);
+                tmem_ld_wait();
+                tmem_ld_use(v0); tmem_ld_use(u0); tmem_ld_use(v1); tmem_ld_use(u1);
 #pragma unroll
-                    for (int i = 0; i < 16; ++i) scr[m * SW + 16 * gq + i] = v[i] + u[i];
+                for (int i = 0; i < 16; ++i) {
+                    scr[tid * SW + 16 * gq + i] = v0[i] + u0[i];
+                    scr[tid * SW + 16 * gq + 16 + i] = v1[i] + u1[i];
                 }
             }
             float v[16], f[16];
-            tmem_ld16(tlane + TM_G + 64, v);
-            tmem_ld16(tlane + TM_F, f);
-            if (lo_rows) {
-                scr[m * SW + 64] = v[0];
+            tmem_ld16_nowait(tlane + TM_G + 64, v);
+            tmem_ld16_nowait(tlane + TM_F, f);
+            tmem_ld_wait();
+            tmem_ld_use(v); tmem_ld_use(f);
+            scr[tid * SW + 64] = v[0];
 #pragma unroll
-                for (int i = 0; i < 8; ++i) scr[m * SW + 72 + i] = f[i] + f[8 + i];
+            for (int i = 0; i < 8; ++i) scr[tid * SW + 72 + i] = f[i] + f[8 + i];
+        }
+#pragma unroll
+        for (int q = 0; q < A; ++q)
+#pragma unroll
+            for (int c = 0; c < 8; ++c) {
+                float v = gW3[q][c];
+                v += __shfl_xor_sync(0xffffffffu, v, 4);
+                v += __shfl_xor_sync(0xffffffffu, v, 8);
+                v += __shfl_xor_sync(0xffffffffu, v, 16);
+                if (g == 0) scr2[(q4 * A + q) * H + c0 + 8 * (c >> 1) + 2 * p + (c & 1)] = v;
             }
-        }
-        __syncthreads();
-        if (tid < 64) {
-#pragma unroll
-            for (int gq = 0; gq < 4; ++gq) {
-                float v[16], u[16];
-                tmem_ld16(tlane + TM_G + 16 * gq, v);
-                tmem_ld16(tlane + TM_G + 96 + 16 * gq, u);
-#pragma unroll
-                for (int i = 0; i < 16; ++i) scr[tid * SW + 16 * gq + i] += v[i] + u[i];
-            }
-            float v[16], f[16];
-            tmem_ld16(tlane + TM_G + 64, v);
-            tmem_ld16(tlane + TM_F, f);
-            scr[tid * SW + 64] += v[0];
-#pragma unroll
-            for (int i = 0; i < 8; ++i) scr[tid * SW + 72 + i] += f[i] + f[8 + i];
-        }
-        __syncthreads();
-        for (int e = tid; e < H * H; e += NT) out[L.off_w2() + e] = scr[(e >> 6) * SW + (e & 63)];
-        if (tid < H) {
-            out[L.off_b2() + tid] = scr[tid * SW + 64];  // G[:, 64]  (ones column)
-            out[L.off_b1() + tid] = scr[tid * SW + 72];  // F[:, 0]
-        }
-        for (int e = tid; e < H * O; e += NT) out[L.off_w1() + e] = scr[(e / O) * SW + 73 + (e % O)];
-        __syncthreads();
-        // dW3: sum the register accumulators over the 8 row groups of the warp, then over the 4 row quadrants
         {
-#pragma unroll
-            for (int q = 0; q < A; ++q)
-#pragma unroll
-                for (int c = 0; c < 8; ++c) {
-                    float v = gW3[q][c];
-                    v += __shfl_xor_sync(0xffffffffu, v, 4);
-                    v += __shfl_xor_sync(0xffffffffu, v, 8);
-                    v += __shfl_xor_sync(0xffffffffu, v, 16);
-                    if (g == 0) scr[(q4 * A + q) * H + c0 + 8 * (c >> 1) + 2 * p + (c & 1)] = v;
-                }
-            __syncthreads();
-            for (int col = tid; col < A * H; col += NT)
-                out[L.off_w3() + col] = (scr[col] + scr[A * H + col]) + (scr[2 * A * H + col] + scr[3 * A * H + col]);
-            __syncthreads();
-        }
-        // row-owned scalars: every row's loss was computed by 4 threads; count one of them
-        {
-            constexpr int NS = A + 1 + 5;
+            // row-owned scalars: every row's loss was computed by 4 threads; count one of them
             float vals[NS];
             const float keep = (hf == 0 && p < 2) ? 1.0f : 0.0f;
 #pragma unroll
@@ -702,18 +709,33 @@ struct Cta {
                 float v = vals[s];
 #pragma unroll
                 for (int o = 16; o > 0; o >>= 1) v += __shfl_down_sync(0xffffffffu, v, o);
-                if (l == 0) scr[s * 8 + w] = v;
+                if (l == 0) scr3[s * 8 + w] = v;
             }
-            __syncthreads();
-            if (tid < NS) {
-                const float sum = (scr[tid * 8] + scr[tid * 8 + 1]) + (scr[tid * 8 + 2] + scr[tid * 8 + 3]);
-                if (tid < A) out[L.off_b3() + tid] = sum;
-                else if (tid == A) out[L.off_logstd()] = sum;
-                else if (with_stats) out[P + (tid - A - 1)] = sum;
-            }
-            if (with_stats && tid >= NS && tid < NS + (MLP_NSTATS - 5)) out[P + 5 + (tid - NS)] = 0.0f;
-            __syncthreads();
         }
+        tc_before_sync();
+        __syncthreads();
+        for (int e = tid; e < H * H; e += NT) {
+            const int m = e >> 6, k = e & 63;
+            out[L.off_w2() + e] = scr[m * SW + k] + scr[(m + 64) * SW + k];
+        }
+        if (tid < H) {
+            out[L.off_b2() + tid] = scr[tid * SW + 64] + scr[(tid + 64) * SW + 64];  // G[:, 64]  (ones column)
+            out[L.off_b1() + tid] = scr[tid * SW + 72] + scr[(tid + 64) * SW + 72];  // F[:, 0]
+        }
+        for (int e = tid; e < H * O; e += NT) {
+            const int m = e / O, o = e % O;
+            out[L.off_w1() + e] = scr[m * SW + 73 + o] + scr[(m + 64) * SW + 73 + o];
+        }
+        for (int col = tid; col < A * H; col += NT)
+            out[L.off_w3() + col] = (scr2[col] + scr2[A * H + col]) + (scr2[2 * A * H + col] + scr2[3 * A * H + col]);
+        if (tid < NS) {
+            const float sum = (scr3[tid * 8] + scr3[tid * 8 + 1]) + (scr3[tid * 8 + 2] + scr3[tid * 8 + 3]);
+            if (tid < A) out[L.off_b3() + tid] = sum;
+            else if (tid == A) out[L.off_logstd()] = sum;
+            else if (with_stats) out[P + (tid - A - 1)] = sum;
+        }
+        if (with_stats && tid >= NS && tid < NS + (MLP_NSTATS - 5)) out[P + 5 + (tid - NS)] = 0.0f;
+        __syncthreads();
         first = true;
         zero_acc();
         stamp(30);
@@ -729,6 +751,7 @@ __global__ void __maxnreg__(120) mlp_train_tc_kernel(const MlpArgs a) {
     cta.stamps = a.timing ? a.timing + (int64_t)blockIdx.x * 32 : nullptr;
     cta.stamp(0);
     if (a.step_counter && blockIdx.x == 0 && threadIdx.x == 0) *a.step_counter += 1ull;
+    cta.prime(a, blockIdx.x, gridDim.x);
     cta.load_weights(a, a.params, [](const float* q) { return __ldg(q); });
     cta.zero_acc();
     cta.stamp(1);

@@ -15,6 +15,7 @@
 // The minibatch shuffle is evaluated on the fly (b2g_perm_apply) or read from the supplied
 // index lists; weights, Adam moments and the step counter are updated in place.
 #include "mlp_tc.cuh"
+#include <stdlib.h>
 
 struct NetLoop {
     MlpArgs a;  // data pointers + loss configuration (params/idx/start/mb/partial are set per step)
@@ -29,10 +30,14 @@ struct NetLoop {
     uint32_t seed_lo, seed_hi;
     float* partial;       // [ctas][P + MLP_NSTATS]
     unsigned int* sync;   // barrier counter, zero at launch
+    long long* timing;    // debug: [ctas][16] clock64 stamps of minibatch step `timing_step` (or NULL)
+    long long* tile_timing;  // debug: [ctas][32] stage stamps of the tiles of that step
+    int timing_step;
 };
 struct LoopArgs {
     NetLoop net[2];
     int n_nets, ctas_per_net;
+    int stagger_cycles;  // the second network starts this many cycles late (see b2g_mlp_train_loop)
 };
 
 __device__ __forceinline__ void net_barrier(unsigned int* ctr, unsigned int target) {
@@ -72,57 +77,100 @@ __device__ __forceinline__ void net_loop(const NetLoop& n, int j, int ctas, uint
     cta.zero_acc();
     cta.load_weights(a, n.params, ld);
     const int64_t steps = (n.B + n.mbs - 1) / n.mbs;
-    for (int e = 0; e < n.epochs; ++e) {
-        a.perm_n = 0;
-        if (n.shuffle == 1) {  // the permutation b2g_permutation(seed, counter = Adam step at epoch start) draws
-            a.perm_n = n.B;
-            a.perm_half_bits = b2g_perm_half_bits(n.B);
-            b2g_perm_keys(n.seed_lo, n.seed_hi, (uint64_t)t, a.perm_keys);
+    int64_t gstep = 0;
+#define LOOP_STAMP(i) do { if (n.timing && tid == 0 && gstep == n.timing_step) n.timing[j * 16 + (i)] = clock64(); } while (0)
+    // minibatch g (0-based, over all epochs) -> its arguments; the shuffle of an epoch is keyed by
+    // the Adam step at the epoch's start (what b2g_permutation(seed, counter_dev = step) reads)
+    const unsigned long long t_begin = t;
+    auto set_step = [&](MlpArgs& m, int64_t gs) {
+        const int64_t e = gs / steps, s = gs % steps;
+        m.start = s * n.mbs;
+        m.mb = (n.B - m.start) < n.mbs ? (n.B - m.start) : n.mbs;
+        m.idx = (n.shuffle == 2) ? n.idx_all + e * n.B + m.start : nullptr;
+        m.perm_n = 0;
+        if (n.shuffle == 1) {
+            m.perm_n = n.B;
+            m.perm_half_bits = b2g_perm_half_bits(n.B);
+            if (s == 0 || gs == 0) b2g_perm_keys(n.seed_lo, n.seed_hi, (uint64_t)(t_begin + e * steps), m.perm_keys);
         }
-        for (int64_t s = 0; s < steps; ++s) {
-            a.start = s * n.mbs;
-            a.mb = (n.B - a.start) < n.mbs ? (n.B - a.start) : n.mbs;
-            a.idx = (n.shuffle == 2) ? n.idx_all + (int64_t)e * n.B + a.start : nullptr;
-            ++t;
-            if (tid == 64) {  // Adam bias corrections of this step, off the critical path
-                const double bc1 = 1.0 - pow(n.beta1, (double)t), bc2 = 1.0 - pow(n.beta2, (double)t);
-                float* adam_c = reinterpret_cast<float*>(smem + OFF_SMALL) + Small<O, A>::END;
-                adam_c[0] = (float)(n.lr / bc1);
-                adam_c[1] = (float)sqrt(bc2);
-            }
-            cta.run_tiles(a, j, ctas);
-            cta.write_partial(out, false);
-            net_barrier(n.sync, ++nbar * (unsigned int)ctas);
-            // ---- fixed-order reduction of this CTA's parameter slice + Adam (reduce_adam_kernel's arithmetic)
-            {
-                const int px = tid & 31, sl = tid >> 5;
-                const int pidx = j * ppc + px;
-                const bool own = px < ppc && pidx < P;
-                float sum = 0.0f;
-                if (own) {
-#pragma unroll 4
-                    for (int b = sl; b < ctas; b += 8) sum += __ldcg(n.partial + (int64_t)b * W + pidx);
-                }
-                scr[sl * 32 + px] = sum;
-                __syncthreads();
-                if (sl == 0 && own) {
-                    float tot = 0.0f;
+    };
+    const int64_t total = steps * n.epochs;
+    const int px = tid & 31, sl = tid >> 5;
+    const int pidx = j * ppc + px;
+    const bool own = px < ppc && pidx < P;
+    if (total > 0) {
+        set_step(a, 0);
+        cta.prime(a, j, ctas);
+    }
+    for (gstep = 0; gstep < total; ++gstep) {
+        ++t;
+        if (tid == 64) {  // Adam bias corrections of this step, off the critical path
+            const double bc1 = 1.0 - pow(n.beta1, (double)t), bc2 = 1.0 - pow(n.beta2, (double)t);
+            float* adam_c = reinterpret_cast<float*>(smem + OFF_SMALL) + Small<O, A>::END;
+            adam_c[0] = (float)(n.lr / bc1);
+            adam_c[1] = (float)sqrt(bc2);
+        }
+        LOOP_STAMP(0);
+        cta.stamps = (n.timing && gstep == n.timing_step) ? n.tile_timing + (int64_t)j * 32 : nullptr;
+        cta.stamp(0);
+        cta.run_tiles(a, j, ctas);
+        cta.stamps = nullptr;
+        LOOP_STAMP(1);
+        const float inv_mb = 1.0f / (float)a.mb;
+        if (gstep + 1 < total) {  // rows of the next minibatch: independent of the update, start them now
+            set_step(a, gstep + 1);
+            cta.prime(a, j, ctas);
+        }
+        // this CTA's slice of the optimiser state, fetched before the wait
+        float mm = 0.0f, vv = 0.0f, pp = 0.0f;
+        if (sl == 0 && own) {
+            mm = n.adam_m[pidx];
+            vv = n.adam_v[pidx];
+            pp = __ldcg(n.params + pidx);
+        }
+        cta.write_partial(out, false);
+        LOOP_STAMP(2);
+        net_barrier(n.sync, ++nbar * (unsigned int)ctas);
+        LOOP_STAMP(3);
+        // ---- fixed-order reduction of this CTA's parameter slice + Adam (reduce_adam_kernel's arithmetic)
+        {
+            // all loads in flight at once (the partials sit in the L2 of either die), summed in a fixed order
+            constexpr int MAXB = 37;  // ceil(2 * 148 / 8)
+            float pv[MAXB];
 #pragma unroll
-                    for (int k = 0; k < 8; ++k) tot += scr[k * 32 + px];
-                    const float* adam_c = reinterpret_cast<const float*>(smem + OFF_SMALL) + Small<O, A>::END;
-                    const float g = tot * (1.0f / (float)a.mb);
-                    const float step_size = adam_c[0], bc2_sqrt = adam_c[1];
-                    float mm = n.adam_m[pidx], vv = n.adam_v[pidx];
-                    mm = mm + (float)(1.0 - n.beta1) * (g - mm);                 // exp_avg.lerp_(grad, 1-beta1)
-                    vv = vv * (float)n.beta2 + ((float)(1.0 - n.beta2) * g) * g;  // mul_(beta2).addcmul_(g, g, 1-beta2)
-                    const float denom = sqrtf(vv) / bc2_sqrt + (float)n.eps;
-                    n.params[pidx] = __ldcg(n.params + pidx) - step_size * (mm / denom);
-                    n.adam_m[pidx] = mm;
-                    n.adam_v[pidx] = vv;
-                }
+            for (int i = 0; i < MAXB; ++i) {
+                const int b = sl + 8 * i;
+                pv[i] = (own && b < ctas) ? __ldcg(n.partial + (int64_t)b * W + pidx) : 0.0f;
             }
-            net_barrier(n.sync, ++nbar * (unsigned int)ctas);
-            cta.load_weights(a, n.params, ld);
+            float sum = 0.0f;
+#pragma unroll
+            for (int i = 0; i < MAXB; ++i) sum += pv[i];
+            scr[sl * 32 + px] = sum;
+            __syncthreads();
+            if (sl == 0 && own) {
+                float tot = 0.0f;
+#pragma unroll
+                for (int k = 0; k < 8; ++k) tot += scr[k * 32 + px];
+                const float* adam_c = reinterpret_cast<const float*>(smem + OFF_SMALL) + Small<O, A>::END;
+                const float g = tot * inv_mb;
+                const float step_size = adam_c[0], bc2_sqrt = adam_c[1];
+                mm = mm + (float)(1.0 - n.beta1) * (g - mm);                 // exp_avg.lerp_(grad, 1-beta1)
+                vv = vv * (float)n.beta2 + ((float)(1.0 - n.beta2) * g) * g;  // mul_(beta2).addcmul_(g, g, 1-beta2)
+                const float denom = sqrtf(vv) / bc2_sqrt + (float)n.eps;
+                n.params[pidx] = pp - step_size * (mm / denom);
+                n.adam_m[pidx] = mm;
+                n.adam_v[pidx] = vv;
+            }
+        }
+        LOOP_STAMP(4);
+        net_barrier(n.sync, ++nbar * (unsigned int)ctas);
+        LOOP_STAMP(5);
+        cta.load_weights(a, n.params, ld);
+        LOOP_STAMP(6);
+        if (n.timing && tid == 0 && gstep == n.timing_step) {
+            unsigned int smid;
+            asm("mov.u32 %0, %%smid;" : "=r"(smid));
+            n.timing[j * 16 + 7] = smid;
         }
     }
     if (j == 0 && tid == 0) *n.step = t;
@@ -134,6 +182,10 @@ __global__ void __maxnreg__(120) train_loop_kernel(const __grid_constant__ LoopA
     extern __shared__ __align__(1024) uint8_t loop_smem_raw[];
     uint8_t* smem = loop_smem_raw;
     const int net = blockIdx.x / args.ctas_per_net, j = blockIdx.x % args.ctas_per_net;
+    if (net == 1 && args.stagger_cycles > 0) {
+        const long long t0 = clock64();
+        while (clock64() - t0 < args.stagger_cycles) __nanosleep(200);
+    }
     if (net == 0 && args.net[0].a.loss_kind != LOSS_VF) net_loop<O, AP>(args.net[0], j, args.ctas_per_net, smem);
     else net_loop<O, 1>(args.net[net], j, args.ctas_per_net, smem);
 }
@@ -157,7 +209,16 @@ static int check_net(const b2g_train_net* t) {
     return B2G_OK;
 }
 
-static void fill_net(NetLoop& n, const b2g_train_net* t, int ctas, float* partial, unsigned int* sync) {
+static long long* g_loop_timing = nullptr;
+static int g_loop_timing_step = 0;
+// debug hook: device buffer [n_nets][ctas][16] of clock64 stamps of one minibatch step
+extern "C" int b2g_mlp_train_loop_debug_timing(long long* buf, int step) {
+    g_loop_timing = buf;
+    g_loop_timing_step = step;
+    return B2G_OK;
+}
+
+static void fill_net(NetLoop& n, const b2g_train_net* t, int ctas, float* partial, unsigned int* sync, int net_index) {
     n = NetLoop{};
     n.a.obs = t->obs; n.a.act = t->act; n.a.adv = t->adv; n.a.old_logp = t->old_logp; n.a.ret = t->ret;
     n.a.loss_kind = t->loss_kind; n.a.flags = t->flags; n.a.clip = t->clip; n.a.ent_coeff = t->ent_coeff;
@@ -170,6 +231,9 @@ static void fill_net(NetLoop& n, const b2g_train_net* t, int ctas, float* partia
     n.seed_lo = (uint32_t)t->shuffle_seed; n.seed_hi = (uint32_t)(t->shuffle_seed >> 32);
     n.partial = partial; n.sync = sync;
     (void)ctas;
+    n.timing = g_loop_timing ? g_loop_timing + (int64_t)net_index * ctas * 16 : nullptr;
+    n.timing_step = g_loop_timing_step;
+    n.tile_timing = g_loop_timing ? g_loop_timing + (int64_t)2 * 296 * 16 + (int64_t)net_index * ctas * 32 : nullptr;
 }
 
 extern "C" int64_t b2g_mlp_train_loop_ws_floats(void) {
@@ -224,12 +288,20 @@ extern "C" int b2g_mlp_train_loop(const b2g_train_net* nets, int n_nets, float* 
     LoopArgs args{};
     args.n_nets = n_nets;
     args.ctas_per_net = grid / n_nets;
+    {
+        static int stagger = -1;
+        if (stagger < 0) {
+            const char* e = getenv("B2G_LOOP_STAGGER");
+            stagger = e ? atoi(e) : 0;
+        }
+        args.stagger_cycles = stagger;
+    }
     unsigned int* sync = reinterpret_cast<unsigned int*>(workspace);
     float* partial = workspace + 64;
     B2G_CUDA(cudaMemsetAsync(sync, 0, 256, s));
     int64_t off = 0;
     for (int i = 0; i < n_nets; ++i) {
-        fill_net(args.net[i], &nets[i], args.ctas_per_net, partial + off, sync + 16 * i);
+        fill_net(args.net[i], &nets[i], args.ctas_per_net, partial + off, sync + 16 * i, i);
         off += (int64_t)args.ctas_per_net *
                (MlpLayout{nets[i].obs_dim, 64, nets[i].out_dim}.total() + MLP_NSTATS);
     }

@@ -294,6 +294,9 @@ typedef struct b2g_train_net {
 int64_t b2g_mlp_train_loop_ws_floats(void);
 int b2g_mlp_train_loop(const b2g_train_net* nets, int n_nets, float* workspace,
                        int64_t workspace_floats, void* stream);
+/* Debug only: device buffer [n_nets][CTAs per network][16] of int64 clock64() stamps of minibatch
+ * step `step` of the next loops (NULL switches it off, the default). */
+int b2g_mlp_train_loop_debug_timing(long long* buf, int step);
 
 /* Debug only: device buffer [grid][32] of int64 that the tcgen05 kernel fills with clock64()
  * stamps of its stages (NULL switches it off, the default). */

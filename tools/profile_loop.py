@@ -1,0 +1,88 @@
+"""Fused training loop alone on the bench workload's shapes: CUDA-event time per minibatch step and
+(--timing) the clock64 stamps of one step."""
+import argparse
+import os
+import sys
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import numpy as np  # noqa: E402
+import torch  # noqa: E402
+
+from garage_b200 import ops  # noqa: E402
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument('--rows', type=int, default=819200)
+    ap.add_argument('--mb', type=int, default=32768)
+    ap.add_argument('--epochs', type=int, default=2)
+    ap.add_argument('--timing', action='store_true')
+    ap.add_argument('--single', action='store_true', help='policy network only')
+    a = ap.parse_args()
+    dev = torch.device('cuda:0')
+    g = torch.Generator(device=dev).manual_seed(0)
+    B = a.rows
+    shape = ops.MlpShape(3, 64, 1, dev)
+    obs = torch.randn(B, 3, device=dev, generator=g)
+    act = torch.randn(B, 1, device=dev, generator=g)
+    adv = torch.randn(B, device=dev, generator=g)
+    olp = torch.randn(B, device=dev, generator=g) * 0.1 - 1.0
+    ret = torch.randn(B, device=dev, generator=g)
+
+    def net(policy):
+        d = dict(shape=shape, params=torch.randn(shape.P, device=dev, generator=g) * 0.1,
+                 adam_m=torch.zeros(shape.P, device=dev), adam_v=torch.zeros(shape.P, device=dev),
+                 step_counter=torch.zeros(1, dtype=torch.int64, device=dev), lr=2.5e-4, beta1=0.9, beta2=0.999,
+                 eps=1e-8, obs=obs, minibatch=a.mb, epochs=a.epochs, shuffle=ops.SHUFFLE_DEVICE, shuffle_seed=1)
+        if policy:
+            d.update(act=act, adv=adv, old_logp=olp, loss_kind=ops.LOSS_PPO)
+        else:
+            d.update(ret=ret, loss_kind=ops.LOSS_VF)
+        return d
+    nets = [net(True)] if a.single else [net(True), net(False)]
+    steps = a.epochs * -(-B // a.mb)
+    ops.mlp_train_loop(nets)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    ops.mlp_train_loop(nets)
+    e1.record()
+    torch.cuda.synchronize()
+    print('loop of {} steps x {} nets: {:.1f} us, {:.2f} us per step'.format(
+        steps, len(nets), 1e3 * e0.elapsed_time(e1), 1e3 * e0.elapsed_time(e1) / steps))
+    if a.timing:
+        lib = ops._lib.load()
+        per = 296 // len(nets)
+        tb = torch.zeros(2 * 296 * 16 + 2 * 296 * 32, dtype=torch.int64, device=dev)
+        lib.b2g_mlp_train_loop_debug_timing(tb.data_ptr(), 5)
+        ops.mlp_train_loop(nets)
+        torch.cuda.synchronize()
+        lib.b2g_mlp_train_loop_debug_timing(None, 0)
+        raw = tb.cpu().numpy()
+        t = raw[:len(nets) * per * 16].reshape(len(nets), per, 16)
+        tiles = raw[2 * 296 * 16:2 * 296 * 16 + len(nets) * per * 32].reshape(len(nets), per, 32)
+        names = ['step start', 'tiles done', 'partial written', 'barrier 1 passed', 'slice reduced + Adam',
+                 'barrier 2 passed', 'weights reloaded']
+        for k in range(len(nets)):
+            tt = t[k]
+            print('--- net', k, ' (median / max cycles since previous stamp; median since start)')
+            for i in range(1, 7):
+                d = tt[:, i] - tt[:, i - 1]
+                print('{:24s} {:8.0f} {:8.0f} {:8.0f}'.format(names[i], np.median(d), d.max(), np.median(tt[:, i] - tt[:, 0])))
+        stage = ['start', '', 'bar4 waited', 'gather published', 'L1 done', 'GEMM1 issued', 'GEMM1 done', 'EPI1 done',
+                 'GEMM2/3 issued', 'GEMM2 done', 'GEMM3 done', 'GEMM4 issued']
+        for k in range(len(nets)):
+            tt = tiles[k]
+            print('--- net', k, 'tile stages (median cycles since previous stamp / since step start)')
+            prev = tt[:, 0]
+            for it in range(2):
+                for q in range(2, 12):
+                    i = q + 10 * it
+                    print('tile{} {:18s} {:8.0f} {:8.0f}'.format(it, stage[q], np.median(tt[:, i] - prev), np.median(tt[:, i] - tt[:, 0])))
+                    prev = tt[:, i]
+        sm = t[:, :, 7]
+        pairs = sum(1 for s in set(sm[0].tolist()) if len(nets) > 1 and s in set(sm[1].tolist()))
+        print('distinct SMs per net:', [len(set(sm[k].tolist())) for k in range(len(nets))], 'SMs hosting both nets:', pairs)
+
+
+if __name__ == '__main__':
+    main()
