@@ -75,7 +75,6 @@ __device__ __forceinline__ void net_loop(const NetLoop& n, int j, int ctas, uint
     float* scr = reinterpret_cast<float*>(smem + OFF_ACT);
     float* out = n.partial + (int64_t)j * W;
     cta.zero_acc();
-    cta.load_weights(a, n.params, ld);
     const int64_t steps = (n.B + n.mbs - 1) / n.mbs;
     int64_t gstep = 0;
 #define LOOP_STAMP(i) do { if (n.timing && tid == 0 && gstep == n.timing_step) n.timing[j * 16 + (i)] = clock64(); } while (0)
@@ -98,29 +97,31 @@ __device__ __forceinline__ void net_loop(const NetLoop& n, int j, int ctas, uint
     const int px = tid & 31, sl = tid >> 5;
     const int pidx = j * ppc + px;
     const bool own = px < ppc && pidx < P;
-    if (total > 0) {
-        set_step(a, 0);
-        cta.prime(a, j, ctas);
-    }
-    for (gstep = 0; gstep < total; ++gstep) {
-        ++t;
-        if (tid == 64) {  // Adam bias corrections of this step, off the critical path
-            const double bc1 = 1.0 - pow(n.beta1, (double)t), bc2 = 1.0 - pow(n.beta2, (double)t);
-            float* adam_c = reinterpret_cast<float*>(smem + OFF_SMALL) + Small<O, A>::END;
-            adam_c[0] = (float)(n.lr / bc1);
-            adam_c[1] = (float)sqrt(bc2);
+    // gstep = -1 is the prologue (prime the first minibatch, load the weights): one call site each
+    // for prime / run_tiles / write_partial / load_weights keeps the loop body small
+    for (gstep = -1; gstep < total; ++gstep) {
+        const bool live = gstep >= 0;
+        if (live) {
+            ++t;
+            if (tid == 64) {  // Adam bias corrections of this step, off the critical path
+                const double bc1 = 1.0 - pow(n.beta1, (double)t), bc2 = 1.0 - pow(n.beta2, (double)t);
+                float* adam_c = reinterpret_cast<float*>(smem + OFF_SMALL) + Small<O, A>::END;
+                adam_c[0] = (float)(n.lr / bc1);
+                adam_c[1] = (float)sqrt(bc2);
+            }
+            LOOP_STAMP(0);
+            cta.stamps = (n.timing && gstep == n.timing_step) ? n.tile_timing + (int64_t)j * 32 : nullptr;
+            cta.stamp(0);
+            cta.run_tiles(a, j, ctas);
+            cta.stamps = nullptr;
         }
-        LOOP_STAMP(0);
-        cta.stamps = (n.timing && gstep == n.timing_step) ? n.tile_timing + (int64_t)j * 32 : nullptr;
-        cta.stamp(0);
-        cta.run_tiles(a, j, ctas);
-        cta.stamps = nullptr;
         LOOP_STAMP(1);
         const float inv_mb = 1.0f / (float)a.mb;
         if (gstep + 1 < total) {  // rows of the next minibatch: independent of the update, start them now
             set_step(a, gstep + 1);
             cta.prime(a, j, ctas);
         }
+        if (live) {
         // this CTA's slice of the optimiser state, fetched before the wait
         float mm = 0.0f, vv = 0.0f, pp = 0.0f;
         if (sl == 0 && own) {
@@ -165,6 +166,7 @@ __device__ __forceinline__ void net_loop(const NetLoop& n, int j, int ctas, uint
         LOOP_STAMP(4);
         net_barrier(n.sync, ++nbar * (unsigned int)ctas);
         LOOP_STAMP(5);
+        }
         cta.load_weights(a, n.params, ld);
         LOOP_STAMP(6);
         if (n.timing && tid == 0 && gstep == n.timing_step) {
@@ -186,8 +188,12 @@ __global__ void __maxnreg__(120) train_loop_kernel(const __grid_constant__ LoopA
         const long long t0 = clock64();
         while (clock64() - t0 < args.stagger_cycles) __nanosleep(200);
     }
-    if (net == 0 && args.net[0].a.loss_kind != LOSS_VF) net_loop<O, AP>(args.net[0], j, args.ctas_per_net, smem);
-    else net_loop<O, 1>(args.net[net], j, args.ctas_per_net, smem);
+    if constexpr (AP == 1) {  // both networks run the SAME code: one copy in the instruction cache
+        net_loop<O, 1>(args.net[net], j, args.ctas_per_net, smem);
+    } else {
+        if (net == 0 && args.net[0].a.loss_kind != LOSS_VF) net_loop<O, AP>(args.net[0], j, args.ctas_per_net, smem);
+        else net_loop<O, 1>(args.net[net], j, args.ctas_per_net, smem);
+    }
 }
 
 // ------------------------------------------------------------------ host --
