@@ -213,39 +213,71 @@ def timed(fn, steps, barrier):
 
 
 def kernel_rooflines(a, algo, device):
-    """Dominant kernel (fused MLP fwd/loss/bwd, one minibatch launch) and the GAE kernel,
-    each timed alone with CUDA events on the launching stream."""
+    """Dominant kernel (the fused training loop: every minibatch step of both networks in one
+    launch; falls back to the one-minibatch kernel when the loop does not apply) and the GAE
+    kernel, each timed alone with CUDA events on the launching stream."""
     import torch
     from garage_b200 import ops
     hbm, tf, kind = peaks()
-    pol = algo.policy
+    pol, vf = algo.policy, algo._value_function
     B, mb = a.n_envs * a.horizon, min(a.minibatch, a.n_envs * a.horizon)
     g = torch.Generator(device=device).manual_seed(0)
     obs = torch.randn(B, 3, device=device, generator=g)
     act = torch.randn(B, 1, device=device, generator=g)
     adv = torch.randn(B, device=device, generator=g)
     olp = torch.randn(B, device=device, generator=g) * 0.1 - 1.0
-    idx = ops.permutation(B, 0, device=device)
-    kw = algo._policy_kwargs()
-    reps = 50
-    for _ in range(5):
-        ops.mlp_minibatch_grad(pol.mlp_shape, pol.flat, obs, idx=idx[:mb], mb=mb, act=act, adv=adv, old_logp=olp, **kw)
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    e0.record()
-    for r in range(reps):
-        s = (r * mb) % max(B - mb + 1, 1)
-        ops.mlp_minibatch_grad(pol.mlp_shape, pol.flat, obs, idx=idx[s:s + mb], mb=mb, act=act, adv=adv, old_logp=olp, **kw)
-    e1.record()
-    torch.cuda.synchronize()
-    ms = e0.elapsed_time(e1) / reps
+    ret = torch.randn(B, device=device, generator=g)
     O_, H, A = pol.mlp_shape.O, pol.mlp_shape.H, pol.mlp_shape.A
-    flops = 3 * 2 * (O_ * H + H * H + H * A) * mb  # SURVEY 8(d): 3 x forward FLOPs per row
-    ach = flops / (ms * 1e-3) / 1e12
-    mlp = dict(bound='tensor', achieved=ach, peak=tf, unit='TFLOP/s', frac=ach / tf, traffic=None,
-               kernel='mlp_train_kernel<H={},O={},A={},BWD> (fp32 CUDA-core FFMA path)'.format(H, O_, A),
-               us_per_launch=ms * 1e3, rows_per_launch=mb, peak_kind=kind + ' bf16 sustained',
-               note='algorithmic FLOPs = 3 x 2 x (O*H + H*H + H*A) per row; nominal fp32 FFMA peak '
-                    '~74 TFLOP/s at max clock')
+    flops_row = 3 * 2 * (O_ * H + H * H + H * A)  # SURVEY 8(d): 3 x forward FLOPs per row and pass
+    kw = algo._policy_kwargs()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    if algo._fused_applies():
+        def net(owner, policy):
+            d = dict(shape=owner.mlp_shape, params=owner.flat.clone(), adam_m=torch.zeros_like(owner.flat),
+                     adam_v=torch.zeros_like(owner.flat),
+                     step_counter=torch.zeros(1, dtype=torch.int64, device=device), lr=2.5e-4, beta1=0.9,
+                     beta2=0.999, eps=1e-8, obs=obs, minibatch=mb, epochs=a.epochs,
+                     shuffle=ops.SHUFFLE_DEVICE, shuffle_seed=1)
+            d.update(dict(act=act, adv=adv, old_logp=olp, **kw) if policy else dict(ret=ret, loss_kind=ops.LOSS_VF))
+            return d
+        nets = [net(pol, True), net(vf, False)]
+        reps = 5
+        for _ in range(3):
+            ops.mlp_train_loop(nets)
+        e0.record()
+        for _ in range(reps):
+            ops.mlp_train_loop(nets)
+        e1.record()
+        torch.cuda.synchronize()
+        ms = e0.elapsed_time(e1) / reps
+        steps = a.epochs * -(-B // mb)
+        flops = 2 * flops_row * B * a.epochs
+        ach = flops / (ms * 1e-3) / 1e12
+        mlp = dict(bound='tensor', achieved=ach, peak=tf, unit='TFLOP/s', frac=ach / tf, traffic=None,
+                   kernel='train_loop_kernel<O={},A={}> (tcgen05 kind::tf32, 3xTF32 split: the tensor pipe '
+                          'executes 3x the algorithmic FLOPs)'.format(O_, A),
+                   us_per_launch=ms * 1e3, minibatch_steps_per_launch=steps, us_per_minibatch_step=ms * 1e3 / steps,
+                   rows_per_launch=2 * B * a.epochs, peak_kind=kind + ' bf16 sustained',
+                   note='algorithmic FLOPs = 3 x 2 x (O*H + H*H + H*A) per row and pass, both networks; '
+                        'K = 64 contractions issued as M64/128 x N64..160 x K8 MMAs whose ~55-65 cycle '
+                        'instruction floor (tools/ld_probe micro-benchmark), not the FLOP rate, bounds them')
+    else:
+        idx = ops.permutation(B, 0, device=device)
+        reps = 50
+        for _ in range(5):
+            ops.mlp_minibatch_grad(pol.mlp_shape, pol.flat, obs, idx=idx[:mb], mb=mb, act=act, adv=adv, old_logp=olp, **kw)
+        e0.record()
+        for r in range(reps):
+            s = (r * mb) % max(B - mb + 1, 1)
+            ops.mlp_minibatch_grad(pol.mlp_shape, pol.flat, obs, idx=idx[s:s + mb], mb=mb, act=act, adv=adv, old_logp=olp, **kw)
+        e1.record()
+        torch.cuda.synchronize()
+        ms = e0.elapsed_time(e1) / reps
+        ach = flops_row * mb / (ms * 1e-3) / 1e12
+        mlp = dict(bound='tensor', achieved=ach, peak=tf, unit='TFLOP/s', frac=ach / tf, traffic=None,
+                   kernel='mlp minibatch kernel H={},O={},A={} (path {})'.format(H, O_, A, ops.mlp_path()),
+                   us_per_launch=ms * 1e3, rows_per_launch=mb, peak_kind=kind + ' bf16 sustained',
+                   note='algorithmic FLOPs = 3 x 2 x (O*H + H*H + H*A) per row')
     # GAE: inputs larger than L2
     T, N = a.gae_T, a.gae_N
     rew = torch.randn(T, N, device=device, generator=g)

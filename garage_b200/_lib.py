@@ -30,6 +30,14 @@ class TrainNet(ctypes.Structure):
                 ('shuffle_seed', c_uint64), ('idx', P)]
 
 
+MAX_RANKS = 8
+
+
+class TrainComm(ctypes.Structure):
+    """`b2g_train_comm` of include/b2g.h (peer-mapped exchange buffers of the multi-GPU loop)."""
+    _fields_ = [('world', c_int), ('rank', c_int), ('peer_base', P * MAX_RANKS), ('seq_base', c_uint32 * 2)]
+
+
 # name -> (restype, argtypes); mirrors include/b2g.h one to one
 SIGNATURES = {
     'b2g_version': (c_int, []),
@@ -74,6 +82,12 @@ SIGNATURES = {
     'b2g_mlp_train_loop_ws_floats': (c_int64, []),
     'b2g_mlp_train_loop_debug_timing': (c_int, [P, c_int]),
     'b2g_mlp_train_loop': (c_int, [POINTER(TrainNet), c_int, P, c_int64, P]),
+    'b2g_train_comm_bytes': (c_int64, []),
+    'b2g_mlp_train_loop_dist': (c_int, [POINTER(TrainNet), c_int, POINTER(TrainComm), P, c_int64, P]),
+    'b2g_comm_alloc': (c_int, [c_int64, POINTER(c_void_p), ctypes.c_char_p]),
+    'b2g_comm_open': (c_int, [ctypes.c_char_p, POINTER(c_void_p)]),
+    'b2g_comm_close': (c_int, [P]),
+    'b2g_comm_free': (c_int, [P]),
 }
 
 

@@ -16,6 +16,7 @@
 // index lists; weights, Adam moments and the step counter are updated in place.
 #include "mlp_tc.cuh"
 #include <stdlib.h>
+#include <string.h>
 
 struct NetLoop {
     MlpArgs a;  // data pointers + loss configuration (params/idx/start/mb/partial are set per step)
@@ -30,6 +31,11 @@ struct NetLoop {
     uint32_t seed_lo, seed_hi;
     float* partial;       // [ctas][P + MLP_NSTATS]
     unsigned int* sync;   // barrier counter, zero at launch
+    // multi-GPU (one process per GPU): peer-mapped exchange buffers, see b2g_mlp_train_loop_dist
+    float* peer_recv[B2G_MAX_RANKS];        // rank r's receive area of this network: [src rank][parity][COMM_P]
+    unsigned int* peer_flag[B2G_MAX_RANKS]; // rank r's flags of this network: [src rank][COMM_CTAS]
+    int world, rank;
+    unsigned int seq_base;                  // minibatch steps this network has exchanged before this launch
     long long* timing;    // debug: [ctas][16] clock64 stamps of minibatch step `timing_step` (or NULL)
     long long* tile_timing;  // debug: [ctas][32] stage stamps of the tiles of that step
     int timing_step;
@@ -39,6 +45,53 @@ struct LoopArgs {
     int n_nets, ctas_per_net;
     int stagger_cycles;  // the second network starts this many cycles late (see b2g_mlp_train_loop)
 };
+
+constexpr int COMM_P = 4608, COMM_CTAS = 2 * 160;  // per-network capacity of the exchange area (floats, CTAs)
+
+__device__ __forceinline__ void st_sys(float* p, float v) { asm volatile("st.relaxed.sys.global.f32 [%0], %1;" ::"l"(p), "f"(v) : "memory"); }
+__device__ __forceinline__ float ld_sys(const float* p) {
+    float v;
+    asm volatile("ld.relaxed.sys.global.f32 %0, [%1];" : "=f"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ void st_release_sys(unsigned int* p, unsigned int v) {
+    asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ unsigned int ld_acquire_sys(const unsigned int* p) {
+    unsigned int v;
+    asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+
+// All-reduce of one CTA's parameter slice over the ranks, inside the kernel (warp 0 of the CTA):
+// every rank stores its slice sums into every rank's receive area over NVLink (peer-mapped
+// memory), raises a per-(rank, CTA) flag with release semantics, waits for the flags of all
+// source ranks and adds the G contributions in rank order -- every rank obtains the same bits.
+// The receive area is double-buffered on the step parity: a rank can be at most one step ahead.
+__device__ __forceinline__ float slice_allreduce(const NetLoop& n, int j, int px, bool own, int pidx, float tot,
+                                                 unsigned int seq) {
+    const int par = (int)(seq & 1u);
+    if (own) {
+        for (int r = 0; r < n.world; ++r) st_sys(n.peer_recv[r] + ((size_t)(n.rank * 2 + par) * COMM_P + pidx), tot);
+    }
+    __threadfence_system();
+    __syncwarp();
+    if (px < n.world) {
+        st_release_sys(n.peer_flag[px] + (size_t)n.rank * COMM_CTAS + j, seq);
+        const unsigned int* mine = n.peer_flag[n.rank] + (size_t)px * COMM_CTAS + j;
+        unsigned int spin = 0;
+        while ((int)(ld_acquire_sys(mine) - seq) < 0) {
+            if (++spin > (1u << 24)) __trap();  // a lost rank must surface as an error, not as a hung GPU
+        }
+    }
+    __syncwarp();
+    __threadfence_system();
+    float sum = 0.0f;
+    if (own) {
+        for (int r = 0; r < n.world; ++r) sum += ld_sys(n.peer_recv[n.rank] + ((size_t)(r * 2 + par) * COMM_P + pidx));
+    }
+    return sum;
+}
 
 __device__ __forceinline__ void net_barrier(unsigned int* ctr, unsigned int target) {
     __syncthreads();
@@ -116,7 +169,7 @@ __device__ __forceinline__ void net_loop(const NetLoop& n, int j, int ctas, uint
             cta.stamps = nullptr;
         }
         LOOP_STAMP(1);
-        const float inv_mb = 1.0f / (float)a.mb;
+        const float inv_mb = 1.0f / ((float)a.mb * (float)(n.world > 1 ? n.world : 1));  // the minibatch spans all ranks
         if (gstep + 1 < total) {  // rows of the next minibatch: independent of the update, start them now
             set_step(a, gstep + 1);
             cta.prime(a, j, ctas);
@@ -148,19 +201,22 @@ __device__ __forceinline__ void net_loop(const NetLoop& n, int j, int ctas, uint
             for (int i = 0; i < MAXB; ++i) sum += pv[i];
             scr[sl * 32 + px] = sum;
             __syncthreads();
-            if (sl == 0 && own) {
+            if (sl == 0 && (own || n.world > 1)) {
                 float tot = 0.0f;
 #pragma unroll
                 for (int k = 0; k < 8; ++k) tot += scr[k * 32 + px];
-                const float* adam_c = reinterpret_cast<const float*>(smem + OFF_SMALL) + Small<O, A>::END;
-                const float g = tot * inv_mb;
-                const float step_size = adam_c[0], bc2_sqrt = adam_c[1];
-                mm = mm + (float)(1.0 - n.beta1) * (g - mm);                 // exp_avg.lerp_(grad, 1-beta1)
-                vv = vv * (float)n.beta2 + ((float)(1.0 - n.beta2) * g) * g;  // mul_(beta2).addcmul_(g, g, 1-beta2)
-                const float denom = sqrtf(vv) / bc2_sqrt + (float)n.eps;
-                n.params[pidx] = pp - step_size * (mm / denom);
-                n.adam_m[pidx] = mm;
-                n.adam_v[pidx] = vv;
+                if (n.world > 1) tot = slice_allreduce(n, j, px, own, pidx, tot, n.seq_base + (unsigned int)gstep + 1u);
+                if (own) {
+                    const float* adam_c = reinterpret_cast<const float*>(smem + OFF_SMALL) + Small<O, A>::END;
+                    const float g = tot * inv_mb;
+                    const float step_size = adam_c[0], bc2_sqrt = adam_c[1];
+                    mm = mm + (float)(1.0 - n.beta1) * (g - mm);                 // exp_avg.lerp_(grad, 1-beta1)
+                    vv = vv * (float)n.beta2 + ((float)(1.0 - n.beta2) * g) * g;  // mul_(beta2).addcmul_(g, g, 1-beta2)
+                    const float denom = sqrtf(vv) / bc2_sqrt + (float)n.eps;
+                    n.params[pidx] = pp - step_size * (mm / denom);
+                    n.adam_m[pidx] = mm;
+                    n.adam_v[pidx] = vv;
+                }
             }
         }
         LOOP_STAMP(4);
@@ -237,6 +293,7 @@ static void fill_net(NetLoop& n, const b2g_train_net* t, int ctas, float* partia
     n.seed_lo = (uint32_t)t->shuffle_seed; n.seed_hi = (uint32_t)(t->shuffle_seed >> 32);
     n.partial = partial; n.sync = sync;
     (void)ctas;
+    n.world = 1; n.rank = 0; n.seq_base = 0;
     n.timing = g_loop_timing ? g_loop_timing + (int64_t)net_index * ctas * 16 : nullptr;
     n.timing_step = g_loop_timing_step;
     n.tile_timing = g_loop_timing ? g_loop_timing + (int64_t)2 * 296 * 16 + (int64_t)net_index * ctas * 32 : nullptr;
@@ -279,8 +336,18 @@ static int launch_loop(const LoopArgs& args, int grid, cudaStream_t s) {
     return B2G_OK;
 }
 
+extern "C" int64_t b2g_train_comm_bytes(void) {
+    // per network: receive area [ranks][2][COMM_P] floats, then flags [ranks][COMM_CTAS] u32
+    return 2 * ((int64_t)B2G_MAX_RANKS * 2 * COMM_P * 4 + (int64_t)B2G_MAX_RANKS * COMM_CTAS * 4);
+}
+
 extern "C" int b2g_mlp_train_loop(const b2g_train_net* nets, int n_nets, float* workspace,
                                   int64_t workspace_floats, void* stream) {
+    return b2g_mlp_train_loop_dist(nets, n_nets, nullptr, workspace, workspace_floats, stream);
+}
+
+extern "C" int b2g_mlp_train_loop_dist(const b2g_train_net* nets, int n_nets, const b2g_train_comm* comm,
+                                       float* workspace, int64_t workspace_floats, void* stream) {
     B2G_CHECK_ARG(nets && (n_nets == 1 || n_nets == 2), "one or two networks");
     B2G_CHECK_ARG(workspace && workspace_floats >= b2g_mlp_train_loop_ws_floats(), "workspace too small");
     for (int i = 0; i < n_nets; ++i) {
@@ -289,6 +356,10 @@ extern "C" int b2g_mlp_train_loop(const b2g_train_net* nets, int n_nets, float* 
     }
     B2G_CHECK_ARG(n_nets == 1 || nets[0].obs_dim == nets[1].obs_dim, "both networks read the same observations");
     B2G_CHECK_ARG(n_nets == 1 || nets[1].out_dim == 1, "the second network is the value function (out_dim 1)");
+    if (comm && comm->world > 1) {
+        B2G_CHECK_ARG(comm->world <= B2G_MAX_RANKS && comm->rank >= 0 && comm->rank < comm->world, "bad world/rank");
+        for (int r = 0; r < comm->world; ++r) B2G_CHECK_ARG(comm->peer_base[r] != nullptr, "NULL peer buffer");
+    }
     cudaStream_t s = (cudaStream_t)stream;
     const int grid = 2 * b2g_sm_count();
     LoopArgs args{};
@@ -308,6 +379,16 @@ extern "C" int b2g_mlp_train_loop(const b2g_train_net* nets, int n_nets, float* 
     int64_t off = 0;
     for (int i = 0; i < n_nets; ++i) {
         fill_net(args.net[i], &nets[i], args.ctas_per_net, partial + off, sync + 16 * i, i);
+        if (comm && comm->world > 1) {
+            NetLoop& n = args.net[i];
+            n.world = comm->world; n.rank = comm->rank; n.seq_base = comm->seq_base[i];
+            const size_t recv_bytes = (size_t)B2G_MAX_RANKS * 2 * COMM_P * 4, flag_bytes = (size_t)B2G_MAX_RANKS * COMM_CTAS * 4;
+            for (int r = 0; r < comm->world; ++r) {
+                uint8_t* base = reinterpret_cast<uint8_t*>(comm->peer_base[r]) + (size_t)i * (recv_bytes + flag_bytes);
+                n.peer_recv[r] = reinterpret_cast<float*>(base);
+                n.peer_flag[r] = reinterpret_cast<unsigned int*>(base + recv_bytes);
+            }
+        }
         off += (int64_t)args.ctas_per_net *
                (MlpLayout{nets[i].obs_dim, 64, nets[i].out_dim}.total() + MLP_NSTATS);
     }
@@ -345,5 +426,34 @@ extern "C" int b2g_debug_occupancy(void) {
     cudaDeviceGetAttribute(&regs, cudaDevAttrMaxRegistersPerMultiprocessor, dev);
     cudaDeviceGetAttribute(&smem_sm, cudaDevAttrMaxSharedMemoryPerMultiprocessor, dev);
     printf("device: %d registers / SM, %d B shared memory / SM\n", regs, smem_sm);
+    return B2G_OK;
+}
+
+// ---- peer-mapped exchange buffers (CUDA IPC: one process per GPU on one node) ----
+extern "C" int b2g_comm_alloc(int64_t bytes, void** ptr_out, void* handle_out_64) {
+    B2G_CHECK_ARG(bytes > 0 && ptr_out && handle_out_64, "bad arguments");
+    void* p = nullptr;
+    B2G_CUDA(cudaMalloc(&p, (size_t)bytes));
+    B2G_CUDA(cudaMemset(p, 0, (size_t)bytes));
+    cudaIpcMemHandle_t h;
+    B2G_CUDA(cudaIpcGetMemHandle(&h, p));
+    static_assert(sizeof(h) == 64, "cudaIpcMemHandle_t is 64 bytes");
+    memcpy(handle_out_64, &h, 64);
+    *ptr_out = p;
+    return B2G_OK;
+}
+extern "C" int b2g_comm_open(const void* handle_64, void** ptr_out) {
+    B2G_CHECK_ARG(handle_64 && ptr_out, "bad arguments");
+    cudaIpcMemHandle_t h;
+    memcpy(&h, handle_64, 64);
+    B2G_CUDA(cudaIpcOpenMemHandle(ptr_out, h, cudaIpcMemLazyEnablePeerAccess));
+    return B2G_OK;
+}
+extern "C" int b2g_comm_close(void* ptr) {
+    B2G_CUDA(cudaIpcCloseMemHandle(ptr));
+    return B2G_OK;
+}
+extern "C" int b2g_comm_free(void* ptr) {
+    B2G_CUDA(cudaFree(ptr));
     return B2G_OK;
 }

@@ -377,11 +377,12 @@ SHUFFLE_NONE, SHUFFLE_DEVICE, SHUFFLE_IDS = 0, 1, 2
 _loop_ws = {}
 
 
-def mlp_train_loop(nets):
+def mlp_train_loop(nets, comm=None):
     """All minibatch steps of `_train` for one or two networks in one cooperative launch
     (b2g_mlp_train_loop).  `nets`: dicts with shape, params, adam_m, adam_v, step_counter, lr,
     beta1, beta2, eps, obs, [act, adv, old_logp | ret], loss_kind, flags, clip, ent_coeff,
-    min_log_std, max_log_std, minibatch (None = full batch), epochs, shuffle, shuffle_seed, idx."""
+    min_log_std, max_log_std, minibatch (None = full batch), epochs, shuffle, shuffle_seed, idx.
+    `comm`: a `_dist.PeerComm` when several ranks train one model (every rank calls this)."""
     lib = _lib.load()
     arr = (_lib.TrainNet * len(nets))()
     dev = nets[0]['params'].device
@@ -416,7 +417,12 @@ def mlp_train_loop(nets):
     if ws is None or ws.numel() < need:
         ws = _loop_ws[dev] = torch.empty(need, dtype=torch.float32, device=dev)
     with torch.cuda.device(dev):
-        call('b2g_mlp_train_loop', arr, len(nets), ptr(ws), ws.numel(), _stream(ws))
+        if comm is None:
+            call('b2g_mlp_train_loop', arr, len(nets), ptr(ws), ws.numel(), _stream(ws))
+        else:  # multi-GPU: gradients all-reduced inside the kernel over peer-mapped memory
+            call('b2g_mlp_train_loop_dist', arr, len(nets), comm.struct(), ptr(ws), ws.numel(), _stream(ws))
+            comm.advance([t.epochs * -(-t.n_rows // (t.minibatch if 0 < t.minibatch < t.n_rows else t.n_rows))
+                          for t in arr])
 
 
 def adam_step(params, grad, grad_scale, adam_m, adam_v, step_counter, lr, beta1=0.9, beta2=0.999,

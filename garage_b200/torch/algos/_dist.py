@@ -57,3 +57,56 @@ def reduce_logs(s, B, group=None):
     dist.all_reduce(mn, op=dist.ReduceOp.MIN, group=group)
     t[35], t[36] = mx[0], mn[0]
     return t[:-1], t[-1]
+
+
+class PeerComm:
+    """Peer-mapped exchange buffers for the in-kernel gradient all-reduce of the fused training
+    loop (b2g_mlp_train_loop_dist): every rank allocates one buffer (cudaMalloc inside libb2g),
+    the CUDA IPC handles travel through torch.distributed, and each rank maps all peers' buffers.
+    One node only (NVLink / NVSwitch peer access); collective constructor."""
+
+    def __init__(self, device, group=None):
+        import ctypes
+
+        from garage_b200 import _lib
+        lib = _lib.load()
+        self.world, self.rank = dist.get_world_size(group), dist.get_rank(group)
+        if self.world > _lib.MAX_RANKS:
+            raise NotImplementedError('at most {} ranks'.format(_lib.MAX_RANKS))
+        self._lib, self._own, self._peers = lib, ctypes.c_void_p(), []
+        handle = ctypes.create_string_buffer(64)
+        with torch.cuda.device(device):
+            _lib.check(lib.b2g_comm_alloc(int(lib.b2g_train_comm_bytes()), ctypes.byref(self._own), handle),
+                       'b2g_comm_alloc')
+            mine = torch.tensor(list(handle.raw), dtype=torch.uint8, device=device)
+            allh = [torch.empty_like(mine) for _ in range(self.world)]
+            dist.all_gather(allh, mine, group=group)
+            self._c = _lib.TrainComm()
+            self._c.world, self._c.rank = self.world, self.rank
+            for r, h in enumerate(allh):
+                if r == self.rank:
+                    self._c.peer_base[r] = self._own.value
+                    continue
+                p = ctypes.c_void_p()
+                _lib.check(lib.b2g_comm_open(bytes(h.cpu().tolist()), ctypes.byref(p)), 'b2g_comm_open')
+                self._c.peer_base[r] = p.value
+                self._peers.append(p)
+        self._seq = [0, 0]
+        dist.barrier(group=group)  # every buffer is mapped (and still zero) before anyone writes
+
+    def struct(self):
+        self._c.seq_base[0], self._c.seq_base[1] = self._seq[0] & 0xffffffff, self._seq[1] & 0xffffffff
+        return self._c
+
+    def advance(self, steps):
+        for i, s in enumerate(steps):
+            self._seq[i] += int(s)
+
+    def close(self):
+        from garage_b200 import _lib
+        for p in self._peers:
+            _lib.check(self._lib.b2g_comm_close(p), 'b2g_comm_close')
+        self._peers = []
+        if self._own:
+            _lib.check(self._lib.b2g_comm_free(self._own), 'b2g_comm_free')
+            self._own = None

@@ -93,6 +93,7 @@ class VPG(RLAlgorithm):
         if update_mode not in ('auto', 'fused', 'stepwise'):
             raise ValueError("update_mode must be 'auto', 'fused' or 'stepwise'")
         self._update_mode = update_mode
+        self._comm = None
         self.last_stats = {}
 
     @staticmethod
@@ -322,7 +323,7 @@ class VPG(RLAlgorithm):
                 np.random.shuffle(host_ids)
 
     def _fused_applies(self):
-        if self._update_mode == 'stepwise' or self._world() > 1:
+        if self._update_mode == 'stepwise':
             return False
         ok = (self.policy.mlp_shape.H == 64 and self._value_function.mlp_shape.H == 64 and
               ops.mlp_path() == 0)
@@ -360,9 +361,30 @@ class VPG(RLAlgorithm):
         """vpg.py:230-248: all policy minibatches, then all value-function minibatches (the two
         loops touch disjoint state, so the fused path runs them side by side)."""
         if self._fused_applies():
-            ops.mlp_train_loop([self._loop_net(self._policy_optimizer, self.policy, f, True),
-                                self._loop_net(self._vf_optimizer, self._value_function, f, False)])
-            return
+            world, comm = self._world(), None
+            if world > 1:
+                # every rank must run the same number of steps: the minibatch size is global, the
+                # shards must be equally long (fixed-length episodes); otherwise step-wise + NCCL
+                import torch.distributed as dist
+                b = torch.tensor([f.B, -f.B], dtype=torch.int64, device=f.obs.device)
+                dist.all_reduce(b, op=dist.ReduceOp.MAX, group=self._pg)
+                if int(b[0]) != -int(b[1]):
+                    if self._update_mode == 'fused':
+                        raise NotImplementedError("update_mode='fused' needs equally long shards on every rank")
+                    world = 0
+                else:
+                    if self._comm is None:
+                        self._comm = _dist.PeerComm(f.obs.device, self._pg)
+                    comm = self._comm
+            if world:
+                nets = [self._loop_net(self._policy_optimizer, self.policy, f, True),
+                        self._loop_net(self._vf_optimizer, self._value_function, f, False)]
+                if world > 1:
+                    for n in nets:
+                        if n['minibatch']:
+                            n['minibatch'] = max(1, n['minibatch'] // world)  # minibatch_size is the global size
+                ops.mlp_train_loop(nets, comm)
+                return
         self._run_minibatches(self._policy_optimizer, self.policy, f, policy=True)
         self._run_minibatches(self._vf_optimizer, self._value_function, f, policy=False)
 

@@ -292,6 +292,29 @@ typedef struct b2g_train_net {
     const int32_t* idx;
 } b2g_train_net;
 int64_t b2g_mlp_train_loop_ws_floats(void);
+
+/* Multi-GPU form (one process per GPU, env-sharded data parallelism; the reference has no
+ * counterpart).  Every rank runs the same loop on its own shard; per minibatch step the gradient
+ * slices are all-reduced INSIDE the kernel: each CTA stores its slice sums into every rank's
+ * peer-mapped buffer over NVLink, raises a flag and adds the world's contributions in rank order
+ * (bit-identical on all ranks), then applies Adam with 1 / (minibatch * world).  All ranks must
+ * run the same number of steps (equal n_rows, minibatch, epochs).  peer_base[r]: rank r's
+ * exchange buffer of b2g_train_comm_bytes() bytes, zeroed once (b2g_comm_alloc) and mapped into
+ * this process (b2g_comm_open; CUDA IPC); seq_base[i]: minibatch steps network i has run through
+ * these buffers in earlier launches (flags only ever grow). */
+#define B2G_MAX_RANKS 8
+typedef struct b2g_train_comm {
+    int world, rank;
+    void* peer_base[B2G_MAX_RANKS];
+    uint32_t seq_base[2];
+} b2g_train_comm;
+int64_t b2g_train_comm_bytes(void);
+int b2g_mlp_train_loop_dist(const b2g_train_net* nets, int n_nets, const b2g_train_comm* comm,
+                            float* workspace, int64_t workspace_floats, void* stream);
+int b2g_comm_alloc(int64_t bytes, void** ptr_out, void* handle_out_64);
+int b2g_comm_open(const void* handle_64, void** ptr_out);
+int b2g_comm_close(void* ptr);
+int b2g_comm_free(void* ptr);
 int b2g_mlp_train_loop(const b2g_train_net* nets, int n_nets, float* workspace,
                        int64_t workspace_floats, void* stream);
 /* Debug only: device buffer [n_nets][CTAs per network][16] of int64 clock64() stamps of minibatch
