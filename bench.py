@@ -301,6 +301,15 @@ def kernel_rooflines(a, algo, device):
     return mlp, gae
 
 
+def _leave(dist):
+    """End of a multi-rank run: meet the other ranks, then exit without tearing the communicator
+    down (a captured graph still references its NCCL kernels; destroying it first can block)."""
+    dist.barrier()
+    sys.stdout.flush()
+    sys.stderr.flush()
+    os._exit(0)
+
+
 def run_b200(a):
     import torch
     import torch.distributed as dist
@@ -318,11 +327,11 @@ def run_b200(a):
     from garage_b200.torch.algos.graphed import GraphedIteration
     algo, policy, vf, sampler = build_algo(a, rank, world, device)
     B = a.n_envs * a.horizon
-    use_graph = (world == 1) and not a.no_graph
+    use_graph = not a.no_graph  # multi-GPU too: NCCL collectives and the fused loop are capturable
 
     # ---- device-resident throughput ("value"): inputs (weights, env state) live in HBM
     if use_graph:
-        runner = GraphedIteration(algo, B, warmup=1)
+        runner = GraphedIteration(algo, B, warmup=2)
         step = lambda i: runner.enqueue()
     else:
         def step(i):
@@ -367,8 +376,7 @@ def run_b200(a):
 
     if rank != 0:
         if world > 1:
-            dist.barrier()
-            dist.destroy_process_group()
+            _leave(dist)
         return
     mlp_roof, gae_roof = kernel_rooflines(a, algo, device)
     cpu = None
@@ -388,8 +396,7 @@ def run_b200(a):
                 last_stats={k: float(v) for k, v in algo.last_stats.items()})
     print(json.dumps(line), flush=True)
     if world > 1:
-        dist.barrier()
-        dist.destroy_process_group()
+        _leave(dist)
 
 
 def main():

@@ -35,7 +35,7 @@ MAX_RANKS = 8
 
 class TrainComm(ctypes.Structure):
     """`b2g_train_comm` of include/b2g.h (peer-mapped exchange buffers of the multi-GPU loop)."""
-    _fields_ = [('world', c_int), ('rank', c_int), ('peer_base', P * MAX_RANKS), ('seq_base', c_uint32 * 2)]
+    _fields_ = [('world', c_int), ('rank', c_int), ('peer_base', P * MAX_RANKS)]
 
 
 # name -> (restype, argtypes); mirrors include/b2g.h one to one

@@ -32,10 +32,9 @@ struct NetLoop {
     float* partial;       // [ctas][P + MLP_NSTATS]
     unsigned int* sync;   // barrier counter, zero at launch
     // multi-GPU (one process per GPU): peer-mapped exchange buffers, see b2g_mlp_train_loop_dist
-    float* peer_recv[B2G_MAX_RANKS];        // rank r's receive area of this network: [src rank][parity][COMM_P]
-    unsigned int* peer_flag[B2G_MAX_RANKS]; // rank r's flags of this network: [src rank][COMM_CTAS]
+    unsigned long long* peer_recv[B2G_MAX_RANKS];  // rank r's receive area of this network: [src rank][parity][COMM_P] slots
     int world, rank;
-    unsigned int seq_base;                  // minibatch steps this network has exchanged before this launch
+    unsigned int* seq_ptr;                  // device counter: minibatch steps this network has exchanged so far
     long long* timing;    // debug: [ctas][16] clock64 stamps of minibatch step `timing_step` (or NULL)
     long long* tile_timing;  // debug: [ctas][32] stage stamps of the tiles of that step
     int timing_step;
@@ -46,49 +45,44 @@ struct LoopArgs {
     int stagger_cycles;  // the second network starts this many cycles late (see b2g_mlp_train_loop)
 };
 
-constexpr int COMM_P = 4608, COMM_CTAS = 2 * 160;  // per-network capacity of the exchange area (floats, CTAs)
+constexpr int COMM_P = 4608;  // per-network capacity of the exchange area (parameters)
 
-__device__ __forceinline__ void st_sys(float* p, float v) { asm volatile("st.relaxed.sys.global.f32 [%0], %1;" ::"l"(p), "f"(v) : "memory"); }
-__device__ __forceinline__ float ld_sys(const float* p) {
-    float v;
-    asm volatile("ld.relaxed.sys.global.f32 %0, [%1];" : "=f"(v) : "l"(p) : "memory");
-    return v;
+// One exchange slot = {value bits, step sequence number} in ONE 8-byte word: an aligned 8-byte store
+// arrives whole at the peer, so the sequence number doubles as the "data ready" flag and no
+// system-scope fence (a multi-microsecond drain of every outstanding NVLink write) is needed.
+__device__ __forceinline__ void st_slot(unsigned long long* p, float v, unsigned int seq) {
+    asm volatile("st.relaxed.sys.global.v2.b32 [%0], {%1, %2};" ::"l"(p), "r"(__float_as_uint(v)), "r"(seq) : "memory");
 }
-__device__ __forceinline__ void st_release_sys(unsigned int* p, unsigned int v) {
-    asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
-}
-__device__ __forceinline__ unsigned int ld_acquire_sys(const unsigned int* p) {
-    unsigned int v;
-    asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
-    return v;
+__device__ __forceinline__ bool ld_slot(const unsigned long long* p, unsigned int seq, float& v) {
+    unsigned int lo, hi;
+    asm volatile("ld.relaxed.sys.global.v2.b32 {%0, %1}, [%2];" : "=r"(lo), "=r"(hi) : "l"(p) : "memory");
+    v = __uint_as_float(lo);
+    return hi == seq;
 }
 
 // All-reduce of one CTA's parameter slice over the ranks, inside the kernel (warp 0 of the CTA):
-// every rank stores its slice sums into every rank's receive area over NVLink (peer-mapped
-// memory), raises a per-(rank, CTA) flag with release semantics, waits for the flags of all
-// source ranks and adds the G contributions in rank order -- every rank obtains the same bits.
-// The receive area is double-buffered on the step parity: a rank can be at most one step ahead.
-__device__ __forceinline__ float slice_allreduce(const NetLoop& n, int j, int px, bool own, int pidx, float tot,
-                                                 unsigned int seq) {
+// every rank stores {slice sum, seq} into every other rank's receive area over NVLink (peer-mapped
+// memory), polls its own area until the slots of all source ranks carry this step's seq, and adds
+// the contributions in rank order -- every rank obtains the same bits.  The receive area is
+// double-buffered on the step parity: a slot of step s is rewritten at step s+2, which its writer
+// can only reach after the reader's whole network passed the barrier of step s+1, i.e. after the
+// reader consumed step s.
+__device__ __forceinline__ float slice_allreduce(const NetLoop& n, bool own, int pidx, float tot, unsigned int seq) {
+    if (!own) return 0.0f;
     const int par = (int)(seq & 1u);
-    if (own) {
-        for (int r = 0; r < n.world; ++r) st_sys(n.peer_recv[r] + ((size_t)(n.rank * 2 + par) * COMM_P + pidx), tot);
-    }
-    __threadfence_system();
-    __syncwarp();
-    if (px < n.world) {
-        st_release_sys(n.peer_flag[px] + (size_t)n.rank * COMM_CTAS + j, seq);
-        const unsigned int* mine = n.peer_flag[n.rank] + (size_t)px * COMM_CTAS + j;
-        unsigned int spin = 0;
-        while ((int)(ld_acquire_sys(mine) - seq) < 0) {
-            if (++spin > (1u << 24)) __trap();  // a lost rank must surface as an error, not as a hung GPU
-        }
-    }
-    __syncwarp();
-    __threadfence_system();
+    for (int r = 0; r < n.world; ++r)
+        if (r != n.rank) st_slot(n.peer_recv[r] + ((size_t)(n.rank * 2 + par) * COMM_P + pidx), tot, seq);
     float sum = 0.0f;
-    if (own) {
-        for (int r = 0; r < n.world; ++r) sum += ld_sys(n.peer_recv[n.rank] + ((size_t)(r * 2 + par) * COMM_P + pidx));
+    for (int r = 0; r < n.world; ++r) {
+        float v = tot;
+        if (r != n.rank) {
+            const unsigned long long* slot = n.peer_recv[n.rank] + ((size_t)(r * 2 + par) * COMM_P + pidx);
+            unsigned int spin = 0;
+            while (!ld_slot(slot, seq, v)) {
+                if (++spin > (1u << 24)) __trap();  // a lost rank must surface as an error, not as a hung GPU
+            }
+        }
+        sum += v;
     }
     return sum;
 }
@@ -124,6 +118,9 @@ __device__ __forceinline__ void net_loop(const NetLoop& n, int j, int ctas, uint
     auto ld = [](const float* q) { return __ldcg(q); };  // parameters are rewritten by other CTAs: L2 only
     unsigned long long t = *reinterpret_cast<volatile unsigned long long*>(n.step);
     unsigned int nbar = 0;
+    // flags only ever grow: the sequence number continues across launches (kept on the device so that a
+    // captured CUDA graph can be replayed)
+    const unsigned int seq_base = n.world > 1 ? *reinterpret_cast<volatile unsigned int*>(n.seq_ptr) : 0u;
     const int ppc = (P + ctas - 1) / ctas;  // parameters reduced + updated by each CTA (<= 32)
     float* scr = reinterpret_cast<float*>(smem + OFF_ACT);
     float* out = n.partial + (int64_t)j * W;
@@ -201,11 +198,11 @@ __device__ __forceinline__ void net_loop(const NetLoop& n, int j, int ctas, uint
             for (int i = 0; i < MAXB; ++i) sum += pv[i];
             scr[sl * 32 + px] = sum;
             __syncthreads();
-            if (sl == 0 && (own || n.world > 1)) {
+            if (sl == 0 && own) {
                 float tot = 0.0f;
 #pragma unroll
                 for (int k = 0; k < 8; ++k) tot += scr[k * 32 + px];
-                if (n.world > 1) tot = slice_allreduce(n, j, px, own, pidx, tot, n.seq_base + (unsigned int)gstep + 1u);
+                if (n.world > 1) tot = slice_allreduce(n, own, pidx, tot, seq_base + (unsigned int)gstep + 1u);
                 if (own) {
                     const float* adam_c = reinterpret_cast<const float*>(smem + OFF_SMALL) + Small<O, A>::END;
                     const float g = tot * inv_mb;
@@ -231,7 +228,10 @@ __device__ __forceinline__ void net_loop(const NetLoop& n, int j, int ctas, uint
             n.timing[j * 16 + 7] = smid;
         }
     }
-    if (j == 0 && tid == 0) *n.step = t;
+    if (j == 0 && tid == 0) {
+        *n.step = t;
+        if (n.world > 1) *n.seq_ptr = seq_base + (unsigned int)total;
+    }
     cta.fini();
 }
 
@@ -293,7 +293,7 @@ static void fill_net(NetLoop& n, const b2g_train_net* t, int ctas, float* partia
     n.seed_lo = (uint32_t)t->shuffle_seed; n.seed_hi = (uint32_t)(t->shuffle_seed >> 32);
     n.partial = partial; n.sync = sync;
     (void)ctas;
-    n.world = 1; n.rank = 0; n.seq_base = 0;
+    n.world = 1; n.rank = 0; n.seq_ptr = nullptr;
     n.timing = g_loop_timing ? g_loop_timing + (int64_t)net_index * ctas * 16 : nullptr;
     n.timing_step = g_loop_timing_step;
     n.tile_timing = g_loop_timing ? g_loop_timing + (int64_t)2 * 296 * 16 + (int64_t)net_index * ctas * 32 : nullptr;
@@ -336,9 +336,10 @@ static int launch_loop(const LoopArgs& args, int grid, cudaStream_t s) {
     return B2G_OK;
 }
 
+constexpr size_t recv_bytes_c = (size_t)B2G_MAX_RANKS * 2 * COMM_P * 8;
 extern "C" int64_t b2g_train_comm_bytes(void) {
-    // per network: receive area [ranks][2][COMM_P] floats, then flags [ranks][COMM_CTAS] u32
-    return 2 * ((int64_t)B2G_MAX_RANKS * 2 * COMM_P * 4 + (int64_t)B2G_MAX_RANKS * COMM_CTAS * 4);
+    // per network: receive area [ranks][2][COMM_P] slots of 8 bytes; then the two step counters of this rank
+    return (int64_t)(2 * recv_bytes_c + 256);
 }
 
 extern "C" int b2g_mlp_train_loop(const b2g_train_net* nets, int n_nets, float* workspace,
@@ -381,13 +382,16 @@ extern "C" int b2g_mlp_train_loop_dist(const b2g_train_net* nets, int n_nets, co
         fill_net(args.net[i], &nets[i], args.ctas_per_net, partial + off, sync + 16 * i, i);
         if (comm && comm->world > 1) {
             NetLoop& n = args.net[i];
-            n.world = comm->world; n.rank = comm->rank; n.seq_base = comm->seq_base[i];
-            const size_t recv_bytes = (size_t)B2G_MAX_RANKS * 2 * COMM_P * 4, flag_bytes = (size_t)B2G_MAX_RANKS * COMM_CTAS * 4;
-            for (int r = 0; r < comm->world; ++r) {
-                uint8_t* base = reinterpret_cast<uint8_t*>(comm->peer_base[r]) + (size_t)i * (recv_bytes + flag_bytes);
-                n.peer_recv[r] = reinterpret_cast<float*>(base);
-                n.peer_flag[r] = reinterpret_cast<unsigned int*>(base + recv_bytes);
+            {
+                const MlpLayout lay{nets[i].obs_dim, 64, nets[i].out_dim};
+                B2G_CHECK_ARG(lay.total() <= COMM_P, "network larger than the exchange area");
             }
+            n.world = comm->world; n.rank = comm->rank;
+            n.seq_ptr = reinterpret_cast<unsigned int*>(reinterpret_cast<uint8_t*>(comm->peer_base[comm->rank]) +
+                                                        2 * recv_bytes_c) + 16 * i;
+            for (int r = 0; r < comm->world; ++r)
+                n.peer_recv[r] = reinterpret_cast<unsigned long long*>(reinterpret_cast<uint8_t*>(comm->peer_base[r]) +
+                                                                       (size_t)i * recv_bytes_c);
         }
         off += (int64_t)args.ctas_per_net *
                (MlpLayout{nets[i].obs_dim, 64, nets[i].out_dim}.total() + MLP_NSTATS);

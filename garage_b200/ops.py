@@ -421,8 +421,6 @@ def mlp_train_loop(nets, comm=None):
             call('b2g_mlp_train_loop', arr, len(nets), ptr(ws), ws.numel(), _stream(ws))
         else:  # multi-GPU: gradients all-reduced inside the kernel over peer-mapped memory
             call('b2g_mlp_train_loop_dist', arr, len(nets), comm.struct(), ptr(ws), ws.numel(), _stream(ws))
-            comm.advance([t.epochs * -(-t.n_rows // (t.minibatch if 0 < t.minibatch < t.n_rows else t.n_rows))
-                          for t in arr])
 
 
 def adam_step(params, grad, grad_scale, adam_m, adam_v, step_counter, lr, beta1=0.9, beta2=0.999,

@@ -21,7 +21,7 @@ def combine_moments(stats, n, group=None):
     world = world_size(group)
     if world == 1:
         return stats
-    mine = torch.stack([torch.tensor(float(n), dtype=torch.float64, device=stats.device),
+    mine = torch.stack([torch.full((), float(n), dtype=torch.float64, device=stats.device),  # fill kernel: capturable
                         stats[0], stats[1] * (n - 1), stats[2]])
     allv = [torch.empty_like(mine) for _ in range(world)]
     dist.all_gather(allv, mine, group=group)
@@ -46,7 +46,7 @@ def reduce_logs(s, B, group=None):
     per-rank return means (equal shard sizes), max/min the extremes.  `s`: float64 tensor
     [>=40] laid out like VPG._enqueue_iteration's stats; returns (s, B) tensors."""
     world = world_size(group)
-    t = torch.cat([s[:40], torch.tensor([float(B)], dtype=torch.float64, device=s.device)])
+    t = torch.cat([s[:40], torch.full((1,), float(B), dtype=torch.float64, device=s.device)])
     if world == 1:
         return t[:-1], t[-1]
     perf = t[32:39].clone()
@@ -91,16 +91,10 @@ class PeerComm:
                 _lib.check(lib.b2g_comm_open(bytes(h.cpu().tolist()), ctypes.byref(p)), 'b2g_comm_open')
                 self._c.peer_base[r] = p.value
                 self._peers.append(p)
-        self._seq = [0, 0]
         dist.barrier(group=group)  # every buffer is mapped (and still zero) before anyone writes
 
     def struct(self):
-        self._c.seq_base[0], self._c.seq_base[1] = self._seq[0] & 0xffffffff, self._seq[1] & 0xffffffff
         return self._c
-
-    def advance(self, steps):
-        for i, s in enumerate(steps):
-            self._seq[i] += int(s)
 
     def close(self):
         from garage_b200 import _lib

@@ -24,8 +24,9 @@ class GraphedIteration:
                              'max_episode_length (e.g. PendulumEnv)')
         if algo._shuffle != 'device':
             raise ValueError("GraphedIteration needs shuffle='device'")
-        if algo._world() > 1:
-            raise ValueError('multi-GPU iterations run eagerly (NCCL all-reduce between kernels)')
+        if algo._world() > 1 and not algo._fused_applies():
+            raise ValueError('multi-GPU iterations are captured only with the fused training loop '
+                             '(the step-wise path all-reduces between kernels)')
         self._algo, self._batch_size = algo, int(batch_size)
         self._graph = None
         self._stats = None

@@ -94,6 +94,7 @@ class VPG(RLAlgorithm):
             raise ValueError("update_mode must be 'auto', 'fused' or 'stepwise'")
         self._update_mode = update_mode
         self._comm = None
+        self._dist_B = None
         self.last_stats = {}
 
     @staticmethod
@@ -366,9 +367,14 @@ class VPG(RLAlgorithm):
                 # every rank must run the same number of steps: the minibatch size is global, the
                 # shards must be equally long (fixed-length episodes); otherwise step-wise + NCCL
                 import torch.distributed as dist
-                b = torch.tensor([f.B, -f.B], dtype=torch.int64, device=f.obs.device)
-                dist.all_reduce(b, op=dist.ReduceOp.MAX, group=self._pg)
-                if int(b[0]) != -int(b[1]):
+                if f.fixed_len and self._dist_B == f.B:
+                    same = True  # fixed-length batches of the size every rank agreed on before
+                else:
+                    b = torch.tensor([f.B, -f.B], dtype=torch.int64, device=f.obs.device)
+                    dist.all_reduce(b, op=dist.ReduceOp.MAX, group=self._pg)
+                    same = int(b[0]) == -int(b[1])
+                    self._dist_B = f.B if same else None
+                if not same:
                     if self._update_mode == 'fused':
                         raise NotImplementedError("update_mode='fused' needs equally long shards on every rank")
                     world = 0

@@ -300,13 +300,12 @@ int64_t b2g_mlp_train_loop_ws_floats(void);
  * (bit-identical on all ranks), then applies Adam with 1 / (minibatch * world).  All ranks must
  * run the same number of steps (equal n_rows, minibatch, epochs).  peer_base[r]: rank r's
  * exchange buffer of b2g_train_comm_bytes() bytes, zeroed once (b2g_comm_alloc) and mapped into
- * this process (b2g_comm_open; CUDA IPC); seq_base[i]: minibatch steps network i has run through
- * these buffers in earlier launches (flags only ever grow). */
+ * this process (b2g_comm_open; CUDA IPC).  The step sequence numbers the flags carry live in the
+ * rank's own buffer and are advanced by the kernel, so a captured launch can be replayed. */
 #define B2G_MAX_RANKS 8
 typedef struct b2g_train_comm {
     int world, rank;
     void* peer_base[B2G_MAX_RANKS];
-    uint32_t seq_base[2];
 } b2g_train_comm;
 int64_t b2g_train_comm_bytes(void);
 int b2g_mlp_train_loop_dist(const b2g_train_net* nets, int n_nets, const b2g_train_comm* comm,
