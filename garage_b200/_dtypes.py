@@ -284,7 +284,7 @@ class DeviceEpisodeBatch(EpisodeBatch):
         pass
 
     def __init__(self, env_spec, dev, n_eps, n_steps, log_std, tm=None, ep_off=None, t_star=None,
-                 episode_info_consts=None, env_info_consts=None, lengths_host=None):
+                 episode_info_consts=None, env_info_consts=None, lengths_host=None, row_map=None):
         # no validation pass: the fields come from the pack kernels, whose
         # invariants the parity tests check bit-exactly
         self.env_spec = env_spec
@@ -295,6 +295,7 @@ class DeviceEpisodeBatch(EpisodeBatch):
         self.tm = tm
         self.ep_off = ep_off
         self.t_star = t_star
+        self.row_map = row_map  # int32 [t_star+1, N]: packed row of every rollout step (ops.pack_rowmap)
         self._episode_info_consts = dict(episode_info_consts or {})
         self._env_info_consts = dict(env_info_consts or {})
         self._cache = {}

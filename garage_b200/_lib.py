@@ -66,6 +66,9 @@ SIGNATURES = {
     'b2g_pack_index': (c_int, [P, P, P, c_int, c_int, c_int, c_int64, P, P, P, P, P, P, P]),
     'b2g_pack_fields': (c_int, [P, P, P, c_int, c_int64, c_int, POINTER(c_void_p),
                                 POINTER(c_void_p), POINTER(c_int), P]),
+    'b2g_pack_rowmap': (c_int, [P, P, P, c_int, c_int64, P, P]),
+    'b2g_pack_fields_mapped': (c_int, [P, c_int, c_int64, c_int, POINTER(c_void_p), POINTER(c_void_p),
+                                       POINTER(c_int), P]),
     'b2g_mlp_num_partials': (c_int, [c_int, c_int, c_int, c_int, c_int64]),
     'b2g_set_mlp_path': (c_int, [c_int]),
     'b2g_get_mlp_path': (c_int, []),

@@ -206,3 +206,120 @@ extern "C" int b2g_pack_fields(const uint8_t* step_type, const int32_t* ep_len,
     B2G_CHECK_LAUNCH();
     return B2G_OK;
 }
+
+// ---- two-stage field packing: row map + tiled transpose ----------------------------------
+// The scatter above gives every thread its own destination stream (4-byte stores, one episode
+// apart) and only N threads.  The map stage keeps the serial walk (it needs the episode end that
+// lies LATER in time) but only writes one int32 per step, coalesced across n; the copy stage is a
+// shared-memory transpose: a 32 x 32 (t, n) tile is read along n and written along t, where
+// consecutive steps of an episode are consecutive packed rows.
+
+// row_map[t*N + n] = packed row of step (t, n), -1 for steps of unfinished (dropped) episodes
+__global__ void __launch_bounds__(128)
+pack_rowmap_kernel(const uint8_t* __restrict__ st, const int32_t* __restrict__ ep_len,
+                   const int64_t* __restrict__ ep_off, int T_used, int64_t N, int32_t* __restrict__ row_map) {
+    const int64_t n = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (n >= N) return;
+    constexpr int U = 8;
+    int32_t dst_row = -1;
+    for (int t1 = T_used - 1; t1 >= 0; t1 -= U) {
+        uint8_t s[U + 1];  // s[u] = step_type at t1 - u; s[U] is the one below the chunk
+#pragma unroll
+        for (int u = 0; u <= U; ++u) s[u] = (t1 - u >= 0) ? st[(int64_t)(t1 - u) * N + n] : 0;
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+            const int t = t1 - u;
+            if (t < 0) break;
+            const int64_t i = (int64_t)t * N + n;
+            if (s[u] >= ST_TERMINAL) dst_row = (int32_t)(ep_off[i] + ep_len[i] - 1);
+            row_map[i] = dst_row;
+            if (dst_row >= 0) {
+                dst_row -= 1;
+                if (t > 0 && s[u + 1] >= ST_TERMINAL) dst_row = -1;  // the step below ends another episode
+            }
+        }
+    }
+}
+
+extern "C" int b2g_pack_rowmap(const uint8_t* step_type, const int32_t* ep_len, const int64_t* ep_off,
+                               int T_used, int64_t N, int32_t* row_map, void* stream) {
+    B2G_CHECK_ARG(T_used > 0 && N > 0 && (int64_t)T_used * N < (int64_t)1 << 31, "bad shape");
+    B2G_CHECK_ARG(step_type && ep_len && ep_off && row_map, "NULL pointer");
+    pack_rowmap_kernel<<<(unsigned)((N + 127) / 128), 128, 0, (cudaStream_t)stream>>>(step_type, ep_len, ep_off, T_used,
+                                                                                    N, row_map);
+    B2G_CHECK_LAUNCH();
+    return B2G_OK;
+}
+
+constexpr int PT = 32, PN = 32, PW = 4;  // tile: steps x envs; words of a field handled per pass
+__global__ void __launch_bounds__(256)
+pack_fields_mapped_kernel(const int32_t* __restrict__ row_map, int T_used, int64_t N, const PackFields f) {
+    __shared__ uint32_t tile[PT][PN * PW + 1];
+    __shared__ int32_t smap[PT][PN + 1];
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    const int t0 = blockIdx.y * PT;
+    const int64_t n0 = (int64_t)blockIdx.x * PN;
+    const int nn = (int)((N - n0) < PN ? (N - n0) : PN);
+    for (int tt = w; tt < PT; tt += 8) {
+        const int t = t0 + tt;
+        smap[tt][lane] = (t < T_used && lane < nn) ? row_map[(int64_t)t * N + n0 + lane] : -1;
+    }
+    for (int k = 0; k < f.n; ++k) {
+        const int b = f.bytes[k];
+        if (b == 1) {
+            __syncthreads();
+            uint8_t* tb = reinterpret_cast<uint8_t*>(&tile[0][0]);  // [PT][PN + 4] bytes
+            for (int tt = w; tt < PT; tt += 8) {
+                const int t = t0 + tt;
+                if (t < T_used && lane < nn) tb[tt * (PN + 4) + lane] = ((const uint8_t*)f.src[k])[(int64_t)t * N + n0 + lane];
+            }
+            __syncthreads();
+            for (int c = w; c < nn; c += 8) {
+                const int32_t d = smap[lane][c];
+                if (d >= 0) ((uint8_t*)f.dst[k])[d] = tb[lane * (PN + 4) + c];
+            }
+            continue;
+        }
+        const int wds = b >> 2;
+        for (int q0 = 0; q0 < wds; q0 += PW) {
+            const int wc = (wds - q0) < PW ? (wds - q0) : PW;
+            __syncthreads();
+            for (int tt = w; tt < PT; tt += 8) {
+                const int t = t0 + tt;
+                if (t >= T_used) continue;
+                const uint32_t* s = (const uint32_t*)f.src[k] + ((int64_t)t * N + n0) * wds + q0;
+                for (int e = lane; e < nn * wc; e += 32) {
+                    const int nl = e / wc, q = e - nl * wc;
+                    tile[tt][nl * PW + q] = s[(int64_t)nl * wds + q];
+                }
+            }
+            __syncthreads();
+            for (int c = w; c < nn; c += 8) {
+                const int32_t d = smap[lane][c];
+                if (d < 0) continue;
+                uint32_t* o = (uint32_t*)f.dst[k] + (int64_t)d * wds + q0;
+                for (int q = 0; q < wc; ++q) o[q] = tile[lane][c * PW + q];
+            }
+        }
+    }
+}
+
+extern "C" int b2g_pack_fields_mapped(const int32_t* row_map, int T_used, int64_t N, int n_fields,
+                                      const void* const* src, void* const* dst, const int* bytes_per_step,
+                                      void* stream) {
+    B2G_CHECK_ARG(T_used > 0 && N > 0 && row_map, "bad shape");
+    B2G_CHECK_ARG(n_fields >= 0 && n_fields <= PACK_MAX_FIELDS, "too many fields");
+    PackFields f;
+    f.n = n_fields;
+    for (int k = 0; k < n_fields; ++k) {
+        B2G_CHECK_ARG(src[k] && dst[k], "NULL field pointer");
+        B2G_CHECK_ARG(bytes_per_step[k] == 1 || (bytes_per_step[k] > 0 && bytes_per_step[k] % 4 == 0), "field width must be 1 or a multiple of 4 bytes");
+        f.src[k] = src[k]; f.dst[k] = dst[k]; f.bytes[k] = bytes_per_step[k];
+    }
+    if (n_fields == 0) return B2G_OK;
+    const dim3 grid((unsigned)((N + PN - 1) / PN), (unsigned)((T_used + PT - 1) / PT));
+    B2G_CHECK_ARG(grid.y <= 65535, "too many time steps");
+    pack_fields_mapped_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(row_map, T_used, N, f);
+    B2G_CHECK_LAUNCH();
+    return B2G_OK;
+}

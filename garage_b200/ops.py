@@ -270,8 +270,19 @@ def pack_index(step_type, ep_len, last_obs, ws, T_ws, t_star, n_eps):
     return lengths, ep_off, last_observations, ep_env, ep_end
 
 
-def pack_fields(step_type, ep_len, ep_off, t_star, n_steps, fields):
-    """fields: list of time-major tensors [T,N,...]; returns packed [n_steps,...] tensors."""
+def pack_rowmap(step_type, ep_len, ep_off, t_star):
+    """int32 [t_star+1, N]: packed row of every step, -1 for steps of unfinished episodes."""
+    N = step_type.shape[1]
+    row_map = torch.empty((int(t_star) + 1, N), dtype=torch.int32, device=step_type.device)
+    with torch.cuda.device(step_type.device):
+        call('b2g_pack_rowmap', ptr(step_type), ptr(ep_len), ptr(ep_off), int(t_star + 1), int(N), ptr(row_map),
+             _stream(step_type))
+    return row_map
+
+
+def pack_fields(step_type, ep_len, ep_off, t_star, n_steps, fields, row_map=None):
+    """fields: list of time-major tensors [T,N,...]; returns packed [n_steps,...] tensors.
+    `row_map` (pack_rowmap) can be passed to share it between several calls on one rollout."""
     N = step_type.shape[1]
     dev = step_type.device
     outs = []
@@ -279,6 +290,26 @@ def pack_fields(step_type, ep_len, ep_off, t_star, n_steps, fields):
         if not f.is_contiguous() or not f.is_cuda:
             raise ValueError('pack fields must be contiguous CUDA tensors')
         outs.append(torch.empty((n_steps, ) + tuple(f.shape[2:]), dtype=f.dtype, device=dev))
+    if row_map is None:
+        row_map = pack_rowmap(step_type, ep_len, ep_off, t_star)
+    for i in range(0, len(fields), 12):
+        fs, os_ = fields[i:i + 12], outs[i:i + 12]
+        k = len(fs)
+        src = (ctypes.c_void_p * k)(*[f.data_ptr() for f in fs])
+        dst = (ctypes.c_void_p * k)(*[o.data_ptr() for o in os_])
+        nbytes = (ctypes.c_int * k)(*[f.element_size() * int(math.prod(f.shape[2:])) for f in fs])
+        with torch.cuda.device(dev):
+            call('b2g_pack_fields_mapped', ptr(row_map), int(t_star + 1), int(N), k, src, dst, nbytes,
+                 _stream(step_type))
+    return outs
+
+
+def pack_fields_scatter(step_type, ep_len, ep_off, t_star, n_steps, fields):
+    """Single-kernel form (thread per env, scattered stores): the first implementation, kept as the
+    cross-check of the tiled path."""
+    N = step_type.shape[1]
+    dev = step_type.device
+    outs = [torch.empty((n_steps, ) + tuple(f.shape[2:]), dtype=f.dtype, device=dev) for f in fields]
     for i in range(0, len(fields), 12):
         fs, os_ = fields[i:i + 12], outs[i:i + 12]
         k = len(fs)

@@ -212,7 +212,8 @@ class GPUSampler(Sampler):
             fields.append(b.mean)
         if b.success is not None:
             fields.append(b.success)
-        packed = ops.pack_fields(b.step_type, b.ep_len, ep_off, t_star, n_steps, fields)
+        row_map = ops.pack_rowmap(b.step_type, b.ep_len, ep_off, t_star)
+        packed = ops.pack_fields(b.step_type, b.ep_len, ep_off, t_star, n_steps, fields, row_map=row_map)
         dev = DeviceEpisodeBatch._Dev()
         dev.observations, dev.actions, dev.rewards, dev.logp, dev.step_types = packed[:5]
         k = 5
@@ -225,7 +226,7 @@ class GPUSampler(Sampler):
         dev.ep_env, dev.ep_end = ep_env, ep_end
         return DeviceEpisodeBatch(
             env_spec=env.spec, dev=dev, n_eps=n_eps, n_steps=n_steps,
-            log_std=_LazyLogStd(pol._module), tm=b, ep_off=ep_off, t_star=t_star,
+            log_std=_LazyLogStd(pol._module), tm=b, ep_off=ep_off, t_star=t_star, row_map=row_map,
             episode_info_consts=env.episode_info(), env_info_consts=env.env_info_consts(),
             lengths_host=np.full(n_eps, self._max_len(), dtype=np.int64) if static else None)
 

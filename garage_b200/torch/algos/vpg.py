@@ -156,7 +156,7 @@ class VPG(RLAlgorithm):
         else:
             adv_tm, ret_tm = ops.gae_time_major(rew_tm, values, tm.step_type[:T], **kw)
         adv, ret = ops.pack_fields(tm.step_type, tm.ep_len, eps.ep_off, eps.t_star, eps.n_steps,
-                                   [adv_tm, ret_tm])
+                                   [adv_tm, ret_tm], row_map=getattr(eps, 'row_map', None))
         f.obs, f.act, f.rew, f.ret = dev.observations, dev.actions, dev.rewards, ret
         f.old_logp, f.old_mean = dev.logp, dev.mean
         f.old_log_std = ls_dev

@@ -203,6 +203,10 @@ int b2g_rollout(int env_id, const double* params, int max_episode_length,
  *  b2g_pack_fields: scatter up to 12 per-step fields (src [T,N,w] -> dst
  *     [n_steps,w]); bytes_per_step[k] is 1 (uint8) or a multiple of 4.  src/dst/
  *     bytes_per_step are HOST arrays of n_fields entries.
+ *  b2g_pack_rowmap + b2g_pack_fields_mapped: the same result in two stages, for batches
+ *     that pack several field groups from one rollout: row_map[T_used,N] (int32) = packed row
+ *     of every step (-1: step of an unfinished episode, dropped), then a tiled transpose
+ *     through shared memory (reads coalesced along n, writes coalesced along t).
  */
 int64_t b2g_pack_ws_bytes(int T);
 int b2g_pack_plan(const uint8_t* step_type, const int32_t* ep_len, int T, int64_t N,
@@ -214,6 +218,11 @@ int b2g_pack_index(const uint8_t* step_type, const int32_t* ep_len, const float*
 int b2g_pack_fields(const uint8_t* step_type, const int32_t* ep_len, const int64_t* ep_off,
                     int T_used, int64_t N, int n_fields, const void* const* src,
                     void* const* dst, const int* bytes_per_step, void* stream);
+int b2g_pack_rowmap(const uint8_t* step_type, const int32_t* ep_len, const int64_t* ep_off,
+                    int T_used, int64_t N, int32_t* row_map, void* stream);
+int b2g_pack_fields_mapped(const int32_t* row_map, int T_used, int64_t N, int n_fields,
+                           const void* const* src, void* const* dst, const int* bytes_per_step,
+                           void* stream);
 
 /* StochasticPolicy.get_actions sampling (torch/policies/stochastic_policy.py:46-89):
  * act = mean + exp(log_std) * eps, eps = Philox(seed; env_id_offset + i, t_counter),

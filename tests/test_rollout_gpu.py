@@ -159,6 +159,16 @@ def test_rollout_replay_parity(name, H, N, T, max_len):
                                [buf.obs, buf.act, buf.rew, buf.step_type])
         for got, want in zip(outs, packed_o):
             assert np.array_equal(got.cpu().numpy(), want)
+        # tiled (row map + transpose) and single-kernel scatter forms agree, also for a field wider
+        # than one 4-word pass and for a shared row map
+        wide = torch.arange(buf.rew.numel() * 6, dtype=torch.float32, device=dev).reshape(*buf.rew.shape, 6)
+        row_map = ops.pack_rowmap(buf.step_type, buf.ep_len, ep_off, t_star)
+        assert int((row_map >= 0).sum()) == n_steps
+        a1 = ops.pack_fields(buf.step_type, buf.ep_len, ep_off, t_star, n_steps, [wide, buf.step_type, buf.rew],
+                             row_map=row_map)
+        a2 = ops.pack_fields_scatter(buf.step_type, buf.ep_len, ep_off, t_star, n_steps, [wide, buf.step_type, buf.rew])
+        for x, y in zip(a1, a2):
+            assert torch.equal(x, y)
         want_last = np.stack([g['last_obs'][t, n] for t, n in order])
         assert np.array_equal(last_observations.cpu().numpy(), want_last)
 
