@@ -82,6 +82,22 @@ static int launch_mlp_tc(const MlpArgs& a, cudaStream_t s) {
     return B2G_OK;
 }
 
+template <int O, int A>
+static int launch_mlp_eval_tc(const MlpArgs& a, cudaStream_t s) {
+    constexpr size_t smem = tc::smem_bytes<O, A>();
+    static bool configured = false;
+    if (!configured) {
+        B2G_CUDA(cudaFuncSetAttribute(tc::mlp_eval_tc_kernel<O, A>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                      (int)smem));
+        B2G_CUDA(cudaFuncSetAttribute(tc::mlp_eval_tc_kernel<O, A>, cudaFuncAttributePreferredSharedMemoryCarveout,
+                                      cudaSharedmemCarveoutMaxShared));
+        configured = true;
+    }
+    tc::mlp_eval_tc_kernel<O, A><<<mlp_tc_grid(a.mb), tc::NT, smem, s>>>(a);
+    B2G_CHECK_LAUNCH();
+    return B2G_OK;
+}
+
 #define B2G_MLP_SHAPES(X) X(64, 3, 1) X(64, 3, 2) X(64, 4, 1) X(32, 3, 1) X(32, 3, 2) X(32, 4, 1)
 
 static int mlp_unsupported(int O, int H, int A) {
@@ -94,8 +110,8 @@ template <bool BWD>
 static int dispatch_mlp(int O, int H, int A, const MlpArgs& a, cudaStream_t s) {
 #define B2G_CASE(HH, OO, AA)                                                         \
     if (H == HH && O == OO && A == AA) {                                             \
-        if constexpr (BWD && HH == 64) {                                             \
-            if (mlp_path() == 0) return launch_mlp_tc<OO, AA>(a, s);                 \
+        if constexpr (HH == 64) {                                                    \
+            if (mlp_path() == 0) return BWD ? launch_mlp_tc<OO, AA>(a, s) : launch_mlp_eval_tc<OO, AA>(a, s); \
         }                                                                            \
         return launch_mlp<HH, OO, AA, BWD>(a, s);                                    \
     }
@@ -109,7 +125,7 @@ extern "C" int b2g_mlp_num_partials(int obs_dim, int hidden, int out_dim, int ba
                                     int64_t rows) {
 #define B2G_CASE(HH, OO, AA)                                                                   \
     if (hidden == HH && obs_dim == OO && out_dim == AA) {                                      \
-        if (backward && HH == 64 && mlp_path() == 0) return mlp_tc_grid(rows);                 \
+        if (HH == 64 && mlp_path() == 0) return mlp_tc_grid(rows);                             \
         return backward ? mlp_grid<HH, OO, AA, true>(rows) : mlp_grid<HH, OO, AA, false>(rows); \
     }
     B2G_MLP_SHAPES(B2G_CASE)

@@ -264,7 +264,7 @@ __device__ __forceinline__ RowData<O, A> load_row(const MlpArgs& a, int64_t src)
         for (int o = 0; o < O; ++o) d.x[o] = a.obs[src * O + o];
         if (a.loss_kind == LOSS_VF) {
             d.in[A + 2] = a.ret[src];
-        } else {
+        } else if (a.loss_kind != LOSS_NONE) {
 #pragma unroll
             for (int q = 0; q < A; ++q) d.in[q] = a.act[src * A + q];
             d.in[A] = a.adv[src];
@@ -740,6 +740,158 @@ struct Cta {
         zero_acc();
         stamp(30);
     }
+
+    // ---- forward only (baselines, logging passes): rows -> h1 -> GEMM1 -> h2 -> mu -> loss statistics.
+    // Same panels, same GEMM1 and the same per-row loss as run_tiles(); nothing of the backward half.
+    // Exactly one thread evaluates a row (warps 0..3, lanes p < 2), so racc holds every row once.
+    __device__ __forceinline__ void run_tiles_fwd(const MlpArgs& a, int64_t tile0, int64_t stride) {
+        const int64_t ntiles = (a.mb + R - 1) / R;
+        const uint32_t tfrag = tmem + ((uint32_t)(32 * q4) << 16) + TM_D + c0;
+        float w3c[A][8], b2c[8];
+#pragma unroll
+        for (int i = 0; i < 4; ++i)
+#pragma unroll
+            for (int e = 0; e < 2; ++e) {
+                const int c = c0 + 8 * i + 2 * p + e;
+                b2c[2 * i + e] = sB2[c];
+#pragma unroll
+                for (int q = 0; q < A; ++q) w3c[q][2 * i + e] = sW3[q * H + c];
+            }
+        const bool evaluator = hf == 0 && p < 2;
+        const int er = (p & 1) ? rb : ra;  // the row this thread evaluates (if evaluator)
+        int it = 0;
+        for (int64_t tile = tile0; tile < ntiles; tile += stride, ++it) {
+            const uint32_t par = tiles_done & 1;
+            const int64_t m0 = tile * R;
+            if (tid < R) {
+                sSrc[tid] = src_n;
+                *reinterpret_cast<float4*>(sX + tid * 4) = make_float4(row_n.x[0], row_n.x[1], row_n.x[2], row_n.x[3]);
+#pragma unroll
+                for (int i = 0; i < NIN; ++i) sIn[tid * NIN + i] = row_n.in[i];
+            }
+            __syncthreads();
+            if (tid < R) {
+                src_n = sNext[(it & 1) * R + tid];
+                row_n = load_row<O, A>(a, src_n);
+            }
+            {
+                const int pn = w & 1, rbk = w >> 1, j = l & 7, rs = l >> 3, f0 = 32 * pn + 4 * j;
+                float w1[4][O], bb[4];
+#pragma unroll
+                for (int q = 0; q < 4; ++q) {
+                    bb[q] = sB1[f0 + q];
+#pragma unroll
+                    for (int o = 0; o < O; ++o) w1[q][o] = sW1[(f0 + q) * O + o];
+                }
+                uint8_t* hp = smem + OFF_ACT + pn * PANEL;
+                uint8_t* lp = smem + OFF_ACT + (3 + pn) * PANEL;
+#pragma unroll
+                for (int i = 0; i < 4; ++i) {
+                    const int r = 16 * rbk + rs + 4 * i;
+                    const float4 xv = *reinterpret_cast<const float4*>(sX + r * 4);
+                    const float x[4] = {xv.x, xv.y, xv.z, xv.w};
+                    float h[4];
+#pragma unroll
+                    for (int q = 0; q < 4; ++q) {
+                        float z = bb[q];
+#pragma unroll
+                        for (int o = 0; o < O; ++o) z = fmaf(w1[q][o], x[o], z);
+                        h[q] = TC_TANH(z);
+                    }
+                    store_split4(hp, lp, chunk_off(r, j), h);
+                }
+            }
+            fence_async_smem();
+            __syncthreads();
+            if (w == 0) {
+                tc_after_sync();
+                if (elect_one()) {
+                    issue_gemm1(sb, tmem);
+                    umma_commit(bar1);
+                }
+                __syncwarp();
+            }
+            if (tid >= R && tid < 2 * R) {
+                const int64_t t2 = tile + 2 * stride;
+                sNext[((it + 1) & 1) * R + (tid - R)] = t2 < ntiles ? mb_src(a, t2 * R + (tid - R)) : -1;
+            }
+            // the old policy's mean of the evaluated row (KL statistic), fetched behind the MMAs
+            const int64_t esrc = evaluator ? sSrc[er] : -1;
+            float om[A];
+#pragma unroll
+            for (int q = 0; q < A; ++q) om[q] = (esrc >= 0 && a.old_mean) ? a.old_mean[esrc * A + q] : 0.0f;
+            mbar_wait(bar1, par);
+            tc_after_sync();
+            {
+                float z[16];
+                tmem_ld_frag(tfrag, z);
+                float mpa[A], mpb[A];
+#pragma unroll
+                for (int q = 0; q < A; ++q) { mpa[q] = 0.0f; mpb[q] = 0.0f; }
+#pragma unroll
+                for (int i = 0; i < 4; ++i)
+#pragma unroll
+                    for (int e = 0; e < 2; ++e) {
+                        const float ha = TC_TANH(z[4 * i + e] + b2c[2 * i + e]);
+                        const float hb = TC_TANH(z[4 * i + 2 + e] + b2c[2 * i + e]);
+#pragma unroll
+                        for (int q = 0; q < A; ++q) {
+                            mpa[q] = fmaf(w3c[q][2 * i + e], ha, mpa[q]);
+                            mpb[q] = fmaf(w3c[q][2 * i + e], hb, mpb[q]);
+                        }
+                    }
+#pragma unroll
+                for (int q = 0; q < A; ++q) {
+                    mpa[q] += __shfl_xor_sync(0xffffffffu, mpa[q], 1);
+                    mpb[q] += __shfl_xor_sync(0xffffffffu, mpb[q], 1);
+                    mpa[q] += __shfl_xor_sync(0xffffffffu, mpa[q], 2);
+                    mpb[q] += __shfl_xor_sync(0xffffffffu, mpb[q], 2);
+                    if (p == 0) {
+                        sMu[(hf * A + q) * R + ra] = mpa[q];
+                        sMu[(hf * A + q) * R + rb] = mpb[q];
+                    }
+                }
+            }
+            tc_before_sync();  // the next tile's GEMM1 overwrites D: order these TMEM reads before it
+            __syncthreads();
+            if (evaluator && esrc >= 0) {
+                float mu[A], dm[A];
+                MlpRowIn<A> in;
+#pragma unroll
+                for (int q = 0; q < A; ++q) {
+                    mu[q] = sB3[q] + sMu[q * R + er] + sMu[(A + q) * R + er];
+                    dm[q] = 0.0f;
+                    in.act[q] = sIn[er * NIN + q];
+                    in.old_mean[q] = om[q];
+                }
+                in.adv = sIn[er * NIN + A]; in.old_logp = sIn[er * NIN + A + 1]; in.ret = sIn[er * NIN + A + 2];
+                mlp_row_loss<A>(a, in, mu, dist, dm, racc);
+                if (a.mean_out) {
+#pragma unroll
+                    for (int q = 0; q < A; ++q) a.mean_out[(m0 + er) * A + q] = mu[q];
+                }
+            }
+            __syncthreads();  // sIn / sSrc / sMu are rewritten by the next tile
+            ++tiles_done;
+        }
+    }
+
+    // this CTA's statistics row: [P gradients (not written) | MLP_NSTATS statistics]
+    __device__ __forceinline__ void write_stats(float* out) {
+        const int P = MlpLayout{O, H, A}.total();
+        float* scr3 = reinterpret_cast<float*>(smem + OFF_ACT);
+        float vals[5] = {racc.st_loss, racc.st_kl, racc.st_ent, racc.st_clip, racc.st_rows};
+#pragma unroll
+        for (int s = 0; s < 5; ++s) {
+            float v = vals[s];
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) v += __shfl_down_sync(0xffffffffu, v, o);
+            if (l == 0) scr3[s * 8 + w] = v;
+        }
+        __syncthreads();
+        if (tid < 5) out[P + tid] = (scr3[tid * 8] + scr3[tid * 8 + 1]) + (scr3[tid * 8 + 2] + scr3[tid * 8 + 3]);
+        else if (tid < MLP_NSTATS) out[P + tid] = 0.0f;
+    }
 };
 
 template <int O, int A>
@@ -757,6 +909,21 @@ __global__ void __maxnreg__(120) mlp_train_tc_kernel(const MlpArgs a) {
     cta.stamp(1);
     cta.run_tiles(a, blockIdx.x, gridDim.x);
     cta.write_partial(a.partial + (int64_t)blockIdx.x * (L.total() + MLP_NSTATS), true);
+    cta.fini();
+}
+
+// forward-only launch: statistics of the logging passes / value baselines (mean_out)
+template <int O, int A>
+__global__ void __maxnreg__(120) mlp_eval_tc_kernel(const MlpArgs a) {
+    extern __shared__ __align__(1024) uint8_t smem[];
+    const MlpLayout L{O, H, A};
+    Cta<O, A> cta;
+    cta.init(smem);
+    cta.prime(a, blockIdx.x, gridDim.x);
+    cta.load_weights(a, a.params, [](const float* q) { return __ldg(q); });
+    cta.zero_acc();
+    cta.run_tiles_fwd(a, blockIdx.x, gridDim.x);
+    cta.write_stats(a.partial + (int64_t)blockIdx.x * (L.total() + MLP_NSTATS));
     cta.fini();
 }
 }  // namespace tc

@@ -81,6 +81,11 @@ def main():
                     prev = tt[:, i]
         sm = t[:, :, 7]
         pairs = sum(1 for s in set(sm[0].tolist()) if len(nets) > 1 and s in set(sm[1].tolist()))
+        if len(nets) > 1:
+            print('CTA j of both nets on the same SM:', int((sm[0] == sm[1]).sum()), 'of', per)
+            inv = {int(s_): j for j, s_ in enumerate(sm[1].tolist())}
+            print('net-1 CTA sharing the SM of net-0 CTA j:', [inv.get(int(s_), -1) for s_ in sm[0].tolist()])
+            print('SM of net-0 CTA j:', [int(x) for x in sm[0].tolist()])
         print('distinct SMs per net:', [len(set(sm[k].tolist())) for k in range(len(nets))], 'SMs hosting both nets:', pairs)
 
 
