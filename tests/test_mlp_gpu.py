@@ -172,3 +172,54 @@ def test_unsupported_shape_fails_loudly():
     from garage_b200 import ops
     with pytest.raises(NotImplementedError):
         ops.MlpShape(5, 64, 1, torch.device('cuda:0'))
+
+
+@pytest.mark.parametrize('Od,A,n', [(3, 1, 64), (3, 2, 1000), (4, 1, 20001), (3, 1, 1)])
+def test_forward_tensor_core_vs_oracle_and_cuda_core(Od, A, n):
+    """Forward-only passes on the tcgen05 tile pipeline (hidden 64): means and value loss against the
+    float64 oracle, every statistic against the CUDA-core kernel, with an index list and a ragged tail."""
+    from garage_b200 import ops
+    H = 64
+    flat, obs, act, adv, old_logp, ret = make_case(Od, H, A, n, seed=11 + n)
+    rng = np.random.default_rng(n)
+    idx = rng.permutation(n).astype(np.int32)
+    p = O.unflatten_params(flat.astype(np.float64), Od, H, A)
+    mean, _, _ = O.mlp_forward(p, obs)
+    dev = torch.device('cuda:0')
+    sh = ops.MlpShape(Od, H, A, dev)
+    t = lambda a: torch.from_numpy(a).to(dev)
+    old_mean = (mean + 0.1).astype(np.float32)
+    old_ls = torch.tensor([float(flat[0]) - 0.05], dtype=torch.float32, device=dev)
+
+    def run():
+        out = {}
+        mo = torch.empty(n, A, device=dev)
+        nb = ops.mlp_eval(sh, t(flat), t(obs), idx=t(idx), loss_kind=ops.LOSS_NONE, mean_out=mo)
+        out['mean'] = mo.cpu().numpy()
+        st = torch.empty(8, dtype=torch.float64, device=dev)
+        nb = ops.mlp_eval(sh, t(flat), t(obs), idx=t(idx), act=t(act), adv=t(adv), old_logp=t(old_logp),
+                          old_mean=t(old_mean), old_log_std=old_ls, loss_kind=ops.LOSS_PPO, min_log_std=math.log(1e-6))
+        ops.mlp_reduce(sh, nb, 1.0, stats_out=st)
+        out['ppo'] = st.cpu().numpy().copy()
+        if A == 1:
+            nb = ops.mlp_eval(sh, t(flat), t(obs), ret=t(ret), loss_kind=ops.LOSS_VF)
+            ops.mlp_reduce(sh, nb, 1.0, stats_out=st)
+            out['vf'] = st.cpu().numpy().copy()
+        return out
+    prev = ops.mlp_path()
+    try:
+        ops.set_mlp_path(0)
+        tcr = run()
+        ops.set_mlp_path(1)
+        ffr = run()
+    finally:
+        ops.set_mlp_path(prev)
+    assert np.allclose(tcr['mean'], mean[idx], rtol=1e-5, atol=1e-5)
+    for k in tcr:
+        if k == 'mean':
+            continue
+        assert tcr[k][4] == n == ffr[k][4]  # rows counted once
+        assert np.allclose(tcr[k][:5], ffr[k][:5], rtol=1e-5, atol=1e-5 * n), (k, tcr[k], ffr[k])
+    if A == 1:
+        want = O.vf_loss_and_grad(flat, Od, H, obs, ret)[0]
+        assert abs(tcr['vf'][0] / n - want) <= 1e-5 * max(1, abs(want))
