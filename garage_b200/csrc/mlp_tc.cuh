@@ -661,30 +661,31 @@ struct Cta {
         float* scr2 = scr + 128 * SW;  // [4][A*H] dW3 partials | [NS][8] row sums
         constexpr int NS = A + 1 + 5;
         float* scr3 = scr2 + 4 * A * H;
-        if (tid < 128) {
-#pragma unroll
-            for (int gq = 0; gq < 4; gq += 2) {
-                float v0[16], u0[16], v1[16], u1[16];
-                tmem_ld16_nowait(tlane + TM_G + 16 * gq, v0);
-                tmem_ld16_nowait(tlane + TM_G + 96 + 16 * gq, u0);
-                tmem_ld16_nowait(tlane + TM_G + 16 * gq + 16, v1);
-                tmem_ld16_nowait(tlane + TM_G + 96 + 16 * gq + 16, u1);
-                tmem_ld_wait();
-                tmem_ld_use(v0); tmem_ld_use(u0); tmem_ld_use(v1); tmem_ld_use(u1);
-#pragma unroll
-                for (int i = 0; i < 16; ++i) {
-                    scr[tid * SW + 16 * gq + i] = v0[i] + u0[i];
-                    scr[tid * SW + 16 * gq + 16 + i] = v1[i] + u1[i];
-                }
-            }
-            float v[16], f[16];
-            tmem_ld16_nowait(tlane + TM_G + 64, v);
-            tmem_ld16_nowait(tlane + TM_F, f);
+        {
+            // warps w and w + 4 own the same TMEM lanes: each takes half of the columns
+            const int m = tid & 127, gq = 2 * hf;
+            float v0[16], u0[16], v1[16], u1[16];
+            tmem_ld16_nowait(tlane + TM_G + 16 * gq, v0);
+            tmem_ld16_nowait(tlane + TM_G + 96 + 16 * gq, u0);
+            tmem_ld16_nowait(tlane + TM_G + 16 * gq + 16, v1);
+            tmem_ld16_nowait(tlane + TM_G + 96 + 16 * gq + 16, u1);
             tmem_ld_wait();
-            tmem_ld_use(v); tmem_ld_use(f);
-            scr[tid * SW + 64] = v[0];
+            tmem_ld_use(v0); tmem_ld_use(u0); tmem_ld_use(v1); tmem_ld_use(u1);
 #pragma unroll
-            for (int i = 0; i < 8; ++i) scr[tid * SW + 72 + i] = f[i] + f[8 + i];
+            for (int i = 0; i < 16; ++i) {
+                scr[m * SW + 16 * gq + i] = v0[i] + u0[i];
+                scr[m * SW + 16 * gq + 16 + i] = v1[i] + u1[i];
+            }
+            if (hf == 0) {
+                float v[16], f[16];
+                tmem_ld16_nowait(tlane + TM_G + 64, v);
+                tmem_ld16_nowait(tlane + TM_F, f);
+                tmem_ld_wait();
+                tmem_ld_use(v); tmem_ld_use(f);
+                scr[m * SW + 64] = v[0];
+#pragma unroll
+                for (int i = 0; i < 8; ++i) scr[m * SW + 72 + i] = f[i] + f[8 + i];
+            }
         }
 #pragma unroll
         for (int q = 0; q < A; ++q)

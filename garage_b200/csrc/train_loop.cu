@@ -131,19 +131,24 @@ __device__ __forceinline__ void net_loop(const NetLoop& n, int j, int ctas, uint
     // minibatch g (0-based, over all epochs) -> its arguments; the shuffle of an epoch is keyed by
     // the Adam step at the epoch's start (what b2g_permutation(seed, counter_dev = step) reads)
     const unsigned long long t_begin = t;
-    auto set_step = [&](MlpArgs& m, int64_t gs) {
-        const int64_t e = gs / steps, s = gs % steps;
-        m.start = s * n.mbs;
+    // (epoch, step in epoch) of the minibatch prepared next: running counters, no 64-bit divisions
+    const int perm_half_bits = n.shuffle == 1 ? b2g_perm_half_bits(n.B) : 0;
+    int64_t ns_e = 0, ns_s = 0;
+    auto set_next_step = [&](MlpArgs& m) {
+        m.start = ns_s * n.mbs;
         m.mb = (n.B - m.start) < n.mbs ? (n.B - m.start) : n.mbs;
-        m.idx = (n.shuffle == 2) ? n.idx_all + e * n.B + m.start : nullptr;
+        m.idx = (n.shuffle == 2) ? n.idx_all + ns_e * n.B + m.start : nullptr;
         m.perm_n = 0;
         if (n.shuffle == 1) {
             m.perm_n = n.B;
-            m.perm_half_bits = b2g_perm_half_bits(n.B);
-            if (s == 0 || gs == 0) b2g_perm_keys(n.seed_lo, n.seed_hi, (uint64_t)(t_begin + e * steps), m.perm_keys);
+            m.perm_half_bits = perm_half_bits;
+            if (ns_s == 0) b2g_perm_keys(n.seed_lo, n.seed_hi, (uint64_t)(t_begin + ns_e * steps), m.perm_keys);
         }
+        if (++ns_s == steps) { ns_s = 0; ++ns_e; }
     };
     const int64_t total = steps * n.epochs;
+    double b1t = 1.0, b2t = 1.0;  // beta1^t, beta2^t (thread 64 only)
+    if (tid == 64) { b1t = pow(n.beta1, (double)t); b2t = pow(n.beta2, (double)t); }
     const int px = tid & 31, sl = tid >> 5;
     const int pidx = j * ppc + px;
     const bool own = px < ppc && pidx < P;
@@ -153,8 +158,10 @@ __device__ __forceinline__ void net_loop(const NetLoop& n, int j, int ctas, uint
         const bool live = gstep >= 0;
         if (live) {
             ++t;
-            if (tid == 64) {  // Adam bias corrections of this step, off the critical path
-                const double bc1 = 1.0 - pow(n.beta1, (double)t), bc2 = 1.0 - pow(n.beta2, (double)t);
+            if (tid == 64) {  // Adam bias corrections of this step: beta^t as a running product (one pow per launch)
+                b1t *= n.beta1;
+                b2t *= n.beta2;
+                const double bc1 = 1.0 - b1t, bc2 = 1.0 - b2t;
                 float* adam_c = reinterpret_cast<float*>(smem + OFF_SMALL) + Small<O, A>::END;
                 adam_c[0] = (float)(n.lr / bc1);
                 adam_c[1] = (float)sqrt(bc2);
@@ -168,9 +175,11 @@ __device__ __forceinline__ void net_loop(const NetLoop& n, int j, int ctas, uint
         LOOP_STAMP(1);
         const float inv_mb = 1.0f / ((float)a.mb * (float)(n.world > 1 ? n.world : 1));  // the minibatch spans all ranks
         if (gstep + 1 < total) {  // rows of the next minibatch: independent of the update, start them now
-            set_step(a, gstep + 1);
+            set_next_step(a);
+            LOOP_STAMP(8);
             cta.prime(a, j, ctas);
         }
+        LOOP_STAMP(9);
         if (live) {
         // this CTA's slice of the optimiser state, fetched before the wait
         float mm = 0.0f, vv = 0.0f, pp = 0.0f;

@@ -79,6 +79,13 @@ def main():
                     i = q + 10 * it
                     print('tile{} {:18s} {:8.0f} {:8.0f}'.format(it, stage[q], np.median(tt[:, i] - prev), np.median(tt[:, i] - tt[:, 0])))
                     prev = tt[:, i]
+        for k in range(len(nets)):
+            print('--- net', k, 'after tiles: set_step {:.0f}, prime {:.0f}, rest until partial written {:.0f}'.format(
+                np.median(t[k][:, 8] - t[k][:, 1]), np.median(t[k][:, 9] - t[k][:, 8]), np.median(t[k][:, 2] - t[k][:, 9])))
+        for k in range(len(nets)):
+            tt = tiles[k]
+            print('--- net', k, 'write_partial: drain wait {:.0f}, TMEM->smem->global {:.0f} (median cycles)'.format(
+                np.median(tt[:, 29] - tt[:, 28]), np.median(tt[:, 30] - tt[:, 29])))
         sm = t[:, :, 7]
         pairs = sum(1 for s in set(sm[0].tolist()) if len(nets) > 1 and s in set(sm[1].tolist()))
         if len(nets) > 1:
