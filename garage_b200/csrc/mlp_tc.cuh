@@ -231,8 +231,8 @@ template <int O, int A>
 struct Small {  // float offsets inside the small region
     static constexpr int NIN = A + 3;  // act[A], adv, old_logp, ret
     static constexpr int W1 = 0, B1 = W1 + H * O, B2 = B1 + H, W3 = B2 + H, B3 = W3 + A * H,
-                         X = B3 + 4, MU = X + R * 4, IN = MU + 2 * A * R, SRC = IN + R * NIN + (R * NIN) % 2,
-                         NEXT = SRC + 2 * R /* int64[R] */, BARS = NEXT + 4 * R /* int64[2][R] */,
+                         X = B3 + 4, MU = X + R * 4, IN = MU + 2 * A * R /* [2][R][NIN] */, SRC = IN + 2 * R * NIN,
+                         NEXT = SRC + 4 * R /* int64[2][R] */, BARS = NEXT + 4 * R /* int64[2][R] */,
                          TSLOT = BARS + 8 /* 4 x u64 */, END = TSLOT + 4;
 };
 template <int O, int A>
@@ -399,8 +399,58 @@ struct Cta {
         }
     }
 
+    // h1 = tanh(W1 x + b1) of the rows published in sX, into registers: thread (w, l) owns features
+    // f0..f0+3 of rows 16*rbk + rs + 4i (i < 4); store_h1() later writes them as tf32 hi/lo panels
+    // (a quarter-warp writes the 8 chunks of one row: conflict-free)
+    __device__ __forceinline__ void layer1(float (&hreg)[4][4]) const {
+        const int pn = w & 1, rbk = w >> 1, j = l & 7, rs = l >> 3, f0 = 32 * pn + 4 * j;
+        float w1[4][O], bb[4];
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+            bb[q] = sB1[f0 + q];
+#pragma unroll
+            for (int o = 0; o < O; ++o) w1[q][o] = sW1[(f0 + q) * O + o];
+        }
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            const int r = 16 * rbk + rs + 4 * i;
+            const float4 xv = *reinterpret_cast<const float4*>(sX + r * 4);
+            const float x[4] = {xv.x, xv.y, xv.z, xv.w};
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+                float z = bb[q];
+#pragma unroll
+                for (int o = 0; o < O; ++o) z = fmaf(w1[q][o], x[o], z);
+                hreg[i][q] = TC_TANH(z);
+            }
+        }
+    }
+    __device__ __forceinline__ void store_h1(const float (&hreg)[4][4]) const {
+        const int pn = w & 1, rbk = w >> 1, j = l & 7, rs = l >> 3;
+        uint8_t* hp = smem + OFF_ACT + pn * PANEL;
+        uint8_t* lp = smem + OFF_ACT + (3 + pn) * PANEL;
+#pragma unroll
+        for (int i = 0; i < 4; ++i) store_split4(hp, lp, chunk_off(16 * rbk + rs + 4 * i, j), hreg[i]);
+    }
+    // rows of the tile in (src_n, row_n) -> shared memory; then start loading the rows whose ids sit in sNext
+    // (sSrc / sIn are double-buffered on `buf`: the loss stage of the current tile still reads the other half)
+    __device__ __forceinline__ void publish_rows(const MlpArgs& a, int buf) {
+        if (tid < R) {
+            sSrc[buf * R + tid] = src_n;
+            *reinterpret_cast<float4*>(sX + tid * 4) = make_float4(row_n.x[0], row_n.x[1], row_n.x[2], row_n.x[3]);
+#pragma unroll
+            for (int i = 0; i < NIN; ++i) sIn[(buf * R + tid) * NIN + i] = row_n.in[i];
+            src_n = sNext[tid];
+            row_n = load_row<O, A>(a, src_n);
+        }
+    }
+
     // forward + loss + backward of the 64-row tiles tile0, tile0 + stride, ... of minibatch `a`;
-    // gradients accumulate in TMEM (G, F) and registers until write_partial()
+    // gradients accumulate in TMEM (G, F) and registers until write_partial().
+    // Software pipeline over tiles: while the tensor cores run GEMM2/GEMM3 of tile t, the CUDA cores
+    // publish the rows of tile t+1 and evaluate its first layer into registers; the rows of t+2 are in
+    // flight and the ids of t+3.. are computed while GEMM1 runs.  Per tile only the panel stores, the
+    // two epilogues and the MMAs themselves remain on the critical path.
     __device__ __forceinline__ void run_tiles(const MlpArgs& a, int64_t tile0, int64_t stride) {
         const int64_t ntiles = (a.mb + R - 1) / R;
         const uint32_t tfrag = tmem + ((uint32_t)(32 * q4) << 16) + TM_D + c0;
@@ -408,76 +458,38 @@ struct Cta {
         uint8_t* const act_lo = smem + OFF_ACT + (3 + hf) * PANEL;
         uint8_t* const dz_hi = smem + OFF_DZ + hf * PANEL;
         uint8_t* const dz_lo = smem + OFF_DZ + (2 + hf) * PANEL;
-        float w3c[A][8], b2c[8];  // this thread's columns of W3 and b2
-#pragma unroll
-        for (int i = 0; i < 4; ++i)
-#pragma unroll
-            for (int e = 0; e < 2; ++e) {
-                const int c = c0 + 8 * i + 2 * p + e;
-                b2c[2 * i + e] = sB2[c];
-#pragma unroll
-                for (int q = 0; q < A; ++q) w3c[q][2 * i + e] = sW3[q * H + c];
-            }
+        float hreg[4][4];
+        if (tile0 < ntiles) {  // prologue: rows and first layer of the first tile
+            publish_rows(a, 0);
+            __syncthreads();
+            layer1(hreg);
+        }
         int it = 0;
         for (int64_t tile = tile0; tile < ntiles; tile += stride, ++it) {
             const uint32_t par = tiles_done & 1;
             const int64_t m0 = tile * R;
             const int valid = (int)((a.mb - m0) < R ? (a.mb - m0) : R);
             const int nks = (valid + 7) >> 3;
+            const bool has_next = tile + stride < ntiles;
             if (tiles_done > 0) mbar_wait(bar4, par ^ 1);  // every MMA of the previous tile has drained
             stamp(2 + 10 * it);
-            // ---- publish this tile's rows; aug panel row = [1 x_hi 0.. | 0 x_lo 0..]; prefetch ahead
+            // ---- h1 panels from registers; aug panel row = [1 x_hi 0.. | 0 x_lo 0..]
+            store_h1(hreg);
             if (tid < R) {
-                sSrc[tid] = src_n;
+                const float4 xv = *reinterpret_cast<const float4*>(sX + tid * 4);
+                const float xs[4] = {xv.x, xv.y, xv.z, xv.w};
                 float xh[8], xl[8];
 #pragma unroll
                 for (int i = 0; i < 8; ++i) { xh[i] = 0.0f; xl[i] = 0.0f; }
                 xh[0] = 1.0f;
 #pragma unroll
-                for (int o = 0; o < O; ++o) split_tf32(row_n.x[o], xh[1 + o], xl[1 + o]);
-                *reinterpret_cast<float4*>(sX + tid * 4) = make_float4(row_n.x[0], row_n.x[1], row_n.x[2], row_n.x[3]);
-#pragma unroll
-                for (int i = 0; i < NIN; ++i) sIn[tid * NIN + i] = row_n.in[i];
+                for (int o = 0; o < O; ++o) split_tf32(xs[o], xh[1 + o], xl[1 + o]);
                 uint8_t* aug = smem + OFF_ACT + 2 * PANEL;
                 const uint32_t o0 = chunk_off(tid, 0), o1 = chunk_off(tid, 2);
                 *reinterpret_cast<float4*>(aug + o0) = make_float4(xh[0], xh[1], xh[2], xh[3]);
                 *reinterpret_cast<float4*>(aug + o0 + 16) = make_float4(xh[4], xh[5], xh[6], xh[7]);
                 *reinterpret_cast<float4*>(aug + o1) = make_float4(xl[0], xl[1], xl[2], xl[3]);
                 *reinterpret_cast<float4*>(aug + o1 + 16) = make_float4(xl[4], xl[5], xl[6], xl[7]);
-            }
-            __syncthreads();
-            if (tid < R) {  // next tile's rows (ids published during the previous tile / before the loop)
-                src_n = sNext[(it & 1) * R + tid];
-                row_n = load_row<O, A>(a, src_n);
-            }
-            stamp(3 + 10 * it);
-            // ---- L1: h1 = tanh(W1 x + b1); a quarter-warp writes the 8 chunks of one row (conflict-free)
-            {
-                const int pn = w & 1, rbk = w >> 1, j = l & 7, rs = l >> 3, f0 = 32 * pn + 4 * j;
-                float w1[4][O], bb[4];
-#pragma unroll
-                for (int q = 0; q < 4; ++q) {
-                    bb[q] = sB1[f0 + q];
-#pragma unroll
-                    for (int o = 0; o < O; ++o) w1[q][o] = sW1[(f0 + q) * O + o];
-                }
-                uint8_t* hp = smem + OFF_ACT + pn * PANEL;
-                uint8_t* lp = smem + OFF_ACT + (3 + pn) * PANEL;
-#pragma unroll
-                for (int i = 0; i < 4; ++i) {
-                    const int r = 16 * rbk + rs + 4 * i;
-                    const float4 xv = *reinterpret_cast<const float4*>(sX + r * 4);
-                    const float x[4] = {xv.x, xv.y, xv.z, xv.w};
-                    float h[4];
-#pragma unroll
-                    for (int q = 0; q < 4; ++q) {
-                        float z = bb[q];
-#pragma unroll
-                        for (int o = 0; o < O; ++o) z = fmaf(w1[q][o], x[o], z);
-                        h[q] = TC_TANH(z);
-                    }
-                    store_split4(hp, lp, chunk_off(r, j), h);
-                }
             }
             stamp(4 + 10 * it);
             fence_async_smem();
@@ -493,13 +505,14 @@ struct Cta {
             stamp(5 + 10 * it);
             if (tid >= R && tid < 2 * R) {  // row ids of the tile after next, off the critical path
                 const int64_t t2 = tile + 2 * stride;
-                sNext[((it + 1) & 1) * R + (tid - R)] = t2 < ntiles ? mb_src(a, t2 * R + (tid - R)) : -1;
+                sNext[tid - R] = t2 < ntiles ? mb_src(a, t2 * R + (tid - R)) : -1;
             }
             mbar_wait(bar1, par);
             tc_after_sync();
             stamp(6 + 10 * it);
             // ---- EPI1: h2, mu, loss, dz2
             float h2[16];  // [4i + 2*row + e]
+            float w3c[A][8];  // this thread's columns of W3
             {
                 float z[16];
                 tmem_ld_frag(tfrag, z);
@@ -507,11 +520,19 @@ struct Cta {
 #pragma unroll
                 for (int q = 0; q < A; ++q) { mpa[q] = 0.0f; mpb[q] = 0.0f; }
 #pragma unroll
-                for (int i = 0; i < 4; ++i)
+                for (int i = 0; i < 4; ++i) {
+                    const float2 b2v = *reinterpret_cast<const float2*>(sB2 + c0 + 8 * i + 2 * p);
+                    const float b2c[2] = {b2v.x, b2v.y};
+#pragma unroll
+                    for (int q = 0; q < A; ++q) {
+                        const float2 wv = *reinterpret_cast<const float2*>(sW3 + q * H + c0 + 8 * i + 2 * p);
+                        w3c[q][2 * i] = wv.x;
+                        w3c[q][2 * i + 1] = wv.y;
+                    }
 #pragma unroll
                     for (int e = 0; e < 2; ++e) {
-                        const float ha = TC_TANH(z[4 * i + e] + b2c[2 * i + e]);
-                        const float hb = TC_TANH(z[4 * i + 2 + e] + b2c[2 * i + e]);
+                        const float ha = TC_TANH(z[4 * i + e] + b2c[e]);
+                        const float hb = TC_TANH(z[4 * i + 2 + e] + b2c[e]);
                         h2[4 * i + e] = ha;
                         h2[4 * i + 2 + e] = hb;
 #pragma unroll
@@ -520,6 +541,7 @@ struct Cta {
                             mpb[q] = fmaf(w3c[q][2 * i + e], hb, mpb[q]);
                         }
                     }
+                }
 #pragma unroll
                 for (int q = 0; q < A; ++q) {
                     mpa[q] += __shfl_xor_sync(0xffffffffu, mpa[q], 1);
@@ -545,11 +567,13 @@ struct Cta {
                         mu[q] = sB3[q] + sMu[q * R + r] + sMu[(A + q) * R + r];
                         dm[q] = 0.0f;
                     }
-                    if (sSrc[r] >= 0) {
+                    const int cb = (it & 1) * R;
+                    if (sSrc[cb + r] >= 0) {
+                        const float* rin = sIn + (cb + r) * NIN;
                         MlpRowIn<A> in;
 #pragma unroll
-                        for (int q = 0; q < A; ++q) { in.act[q] = sIn[r * NIN + q]; in.old_mean[q] = 0.0f; }
-                        in.adv = sIn[r * NIN + A]; in.old_logp = sIn[r * NIN + A + 1]; in.ret = sIn[r * NIN + A + 2];
+                        for (int q = 0; q < A; ++q) { in.act[q] = rin[q]; in.old_mean[q] = 0.0f; }
+                        in.adv = rin[A]; in.old_logp = rin[A + 1]; in.ret = rin[A + 2];
                         mlp_row_loss<A>(a, in, mu, dist, dm, racc);
                     }
 #pragma unroll
@@ -579,22 +603,35 @@ struct Cta {
                     store_split2(dz_hi, dz_lo, pair_off(rb, i, p), dz[2], dz[3]);
                 }
             }
+            if (has_next) publish_rows(a, (it + 1) & 1);  // rows of the next tile (the other sIn / sSrc half)
             stamp(7 + 10 * it);
             fence_async_smem();
             tc_before_sync();
             __syncthreads();
+            // ---- the tensor cores take over: warp 0 issues GEMM2 (its lanes are held back by the
+            // tensor-pipe queue meanwhile); every warp evaluates the first layer of the next tile into
+            // registers; warp 4 then issues GEMM3 (weight gradients: nobody waits for it before the
+            // dz1 store), so that no single warp carries both issue sequences.
             if (w == 0) {
                 tc_after_sync();
                 if (elect_one()) {
                     issue_gemm2(sb, tmem);
                     umma_commit(bar2);
+                }
+                __syncwarp();
+            }
+            stamp(8 + 10 * it);
+            if (has_next) layer1(hreg);
+            if (w == 4) {
+                tc_after_sync();
+                if (elect_one()) {
                     issue_gemm3(sb, tmem, first, nks);
                     umma_commit(bar3);
                 }
                 __syncwarp();
             }
+            stamp(3 + 10 * it);
             // ---- EPI2: dz1 = dh1 (1 - h1^2)
-            stamp(8 + 10 * it);
             mbar_wait(bar2, par);
             tc_after_sync();
             stamp(9 + 10 * it);

@@ -68,16 +68,19 @@ def main():
             for i in range(1, 7):
                 d = tt[:, i] - tt[:, i - 1]
                 print('{:24s} {:8.0f} {:8.0f} {:8.0f}'.format(names[i], np.median(d), d.max(), np.median(tt[:, i] - tt[:, 0])))
-        stage = ['start', '', 'bar4 waited', 'gather published', 'L1 done', 'GEMM1 issued', 'GEMM1 done', 'EPI1 done',
-                 'GEMM2/3 issued', 'GEMM2 done', 'GEMM3 done', 'GEMM4 issued']
+        # stamp ids of run_tiles in program order
+        order = [2, 4, 5, 6, 7, 8, 3, 9, 10, 11]
+        stage = {2: 'bar4 waited', 4: 'h1 + aug panels stored', 5: 'GEMM1 issued', 6: 'GEMM1 done',
+                 7: 'EPI1 done (+ next rows published)', 8: 'GEMM2 issued', 3: 'next L1 (+ GEMM3 issue) done',
+                 9: 'GEMM2 done', 10: 'EPI2 math + GEMM3 done', 11: 'dz1 stored, GEMM4 issued'}
         for k in range(len(nets)):
             tt = tiles[k]
             print('--- net', k, 'tile stages (median cycles since previous stamp / since step start)')
             prev = tt[:, 0]
             for it in range(2):
-                for q in range(2, 12):
+                for q in order:
                     i = q + 10 * it
-                    print('tile{} {:18s} {:8.0f} {:8.0f}'.format(it, stage[q], np.median(tt[:, i] - prev), np.median(tt[:, i] - tt[:, 0])))
+                    print('tile{} {:36s} {:8.0f} {:8.0f}'.format(it, stage[q], np.median(tt[:, i] - prev), np.median(tt[:, i] - tt[:, 0])))
                     prev = tt[:, i]
         for k in range(len(nets)):
             print('--- net', k, 'after tiles: set_step {:.0f}, prime {:.0f}, rest until partial written {:.0f}'.format(
