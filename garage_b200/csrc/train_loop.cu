@@ -87,18 +87,19 @@ __device__ __forceinline__ float slice_allreduce(const NetLoop& n, bool own, int
     return sum;
 }
 
+// Barrier over the CTAs of one network (all co-resident): arrive = one release-reduction (no reply
+// to wait for), wait = acquire loads until the count reaches `target`.  bar.sync orders the other
+// threads' writes before thread 0's release and thread 0's acquire before their later reads.
 __device__ __forceinline__ void net_barrier(unsigned int* ctr, unsigned int target) {
     __syncthreads();
     if (threadIdx.x == 0) {
-        __threadfence();
-        atomicAdd(ctr, 1u);
+        asm volatile("red.release.gpu.global.add.u32 [%0], 1;" ::"l"(ctr) : "memory");
         unsigned int v;
         unsigned int spin = 0;
         do {
             asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(ctr) : "memory");
             if (++spin > (1u << 22)) __trap();  // a lost CTA must surface as an error, not as a hung GPU
         } while (v < target);
-        __threadfence();
     }
     __syncthreads();
 }
