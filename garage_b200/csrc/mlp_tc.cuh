@@ -554,7 +554,8 @@ struct Cta {
                     }
                 }
             }
-            __syncthreads();
+            // the two column halves of rows 16*q4 .. 16*q4+15 sit in warps q4 and q4 + 4: only that pair meets
+            asm volatile("bar.sync %0, 64;" ::"r"(1 + q4) : "memory");
             {
                 // the loss of a row is evaluated by the lanes p and p^2 of its quad (p&1 picks the row),
                 // then handed to the other lanes: half the instructions of evaluating both rows everywhere
