@@ -99,6 +99,9 @@ enum : uint32_t { B2G_STREAM_ACTION = 0, B2G_STREAM_RESET = 1, B2G_STREAM_PERM =
 // even-width bit domain >= n, cycle-walked back into [0,n).  Counter based (keys =
 // Philox(seed; counter)): the same (seed, counter) gives the same permutation on any number of
 // ranks, and any kernel can evaluate single elements on the fly (b2g_perm_apply).
+// rounds of the balanced Feistel network (4 = Luby-Rackoff's strong pseudo-random permutation with
+// independent round functions; the id computation sits on the critical path of a minibatch step)
+constexpr int B2G_PERM_ROUNDS = 4;
 __host__ __device__ __forceinline__ uint32_t b2g_mix32(uint32_t x) {
     x ^= x >> 16; x *= 0x85EBCA6Bu; x ^= x >> 13; x *= 0xC2B2AE35u; x ^= x >> 16;
     return x;
@@ -120,7 +123,7 @@ __host__ __device__ __forceinline__ uint64_t b2g_perm_apply(const uint32_t* keys
     do {
         uint32_t L = (uint32_t)(x >> half_bits) & mask, R = (uint32_t)x & mask;
 #pragma unroll
-        for (int r = 0; r < 8; ++r) {
+        for (int r = 0; r < B2G_PERM_ROUNDS; ++r) {
             const uint32_t f = b2g_mix32(R ^ keys[r]) & mask;
             const uint32_t nl = R;
             R = L ^ f;
