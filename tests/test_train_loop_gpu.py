@@ -53,6 +53,23 @@ def test_fused_matches_stepwise_numpy_shuffle_cartpole():
     assert _rel(pf, ps) < 1e-5 and _rel(vf_, vs) < 1e-5
 
 
+@pytest.mark.parametrize('kw', [
+    dict(entropy_method='regularized', policy_ent_coeff=0.02, center_adv=True),
+    dict(entropy_method='regularized', policy_ent_coeff=0.02, use_softplus_entropy=True, stop_entropy_gradient=True),
+    dict(entropy_method='max', policy_ent_coeff=0.01, center_adv=False, stop_entropy_gradient=True),
+    dict(positive_adv=True, center_adv=False),
+])
+def test_fused_matches_stepwise_entropy_and_advantage_options(kw):
+    """The entropy configurations of vpg.py:109-125 / 324-347 / 408-432 and positive_adv (vpg.py:375-377)
+    flow through the fused loop's arguments exactly as through the step-wise path."""
+    from garage_b200.envs import PendulumEnv
+    pf, vf_, sf, lf = _run(PendulumEnv, 'ppo', 'fused', 64, 2, 640, **kw)
+    ps, vs, ss, ls = _run(PendulumEnv, 'ppo', 'stepwise', 64, 2, 640, **kw)
+    assert sf == ss
+    assert _rel(pf, ps) < 1e-5 and _rel(vf_, vs) < 1e-5
+    assert abs(lf['GaussianMLPPolicy/Entropy'] - ls['GaussianMLPPolicy/Entropy']) < 1e-5
+
+
 def test_fused_two_action_dims_pointenv():
     from garage_b200.envs import PointEnv
     pf, vf_, sf, _ = _run(PointEnv, 'ppo', 'fused', 64, 2, 640)
