@@ -111,3 +111,41 @@ def test_graph_replay_matches_eager_full_size():
         torch.cuda.synchronize()
         res.append((policy.flat.clone(), vf.flat.clone()))
     assert torch.equal(res[0][0], res[1][0]) and torch.equal(res[0][1], res[1][1])
+
+
+def test_cartpole_16384_envs_ragged_bookkeeping_full_size():
+    """BASELINE configs[2]: 16,384 CartPole envs, early termination.  Integer bookkeeping at full size:
+    lengths sum to the batch, every episode is FIRST .. (TERMINAL | TIMEOUT), the row map is a bijection
+    onto the packed rows and the packed fields are the mapped time-major ones (bit-exact)."""
+    from garage_b200.envs import CartPoleEnv
+    from garage_b200.sampler import GPUSampler
+    from garage_b200.torch.policies import GaussianMLPPolicy
+    n, t_max = 16384, 200
+    torch.manual_seed(0)
+    env = CartPoleEnv(max_episode_length=t_max)
+    policy = GaussianMLPPolicy(env.spec, hidden_sizes=(64, 64))
+    sampler = GPUSampler(policy, env, max_episode_length=t_max, n_envs=n, seed=5)
+    eps = sampler.obtain_samples(0, n * t_max, policy)
+    lengths = eps.dev.lengths
+    assert int(lengths.sum()) == eps.n_steps >= n * t_max and lengths.numel() == eps.n_episodes
+    assert int(lengths.min()) >= 1 and int(lengths.max()) <= t_max
+    st = eps.dev.step_types.long()
+    ends = torch.cumsum(lengths, 0) - 1
+    starts = ends - lengths + 1
+    is_end = torch.zeros(eps.n_steps, dtype=torch.bool, device=st.device)
+    is_end[ends] = True
+    assert bool((st[ends] >= 2).all()) and bool((st[~is_end] <= 1).all())       # TERMINAL/TIMEOUT only at the ends
+    multi = lengths > 1
+    assert bool((st[starts[multi]] == 0).all())                                 # FIRST (a 1-step episode is TERMINAL)
+    assert bool((st[ends[lengths == t_max]] == 3).all())                        # the time limit wins: TIMEOUT
+    assert bool((st[ends[lengths < t_max]] == 2).all())                         # early end: TERMINAL
+    rm = eps.row_map
+    valid = rm >= 0
+    assert int(valid.sum()) == eps.n_steps
+    assert torch.equal(torch.sort(rm[valid].long())[0], torch.arange(eps.n_steps, device=rm.device))
+    rows = rm[valid].long()
+    tm = eps.tm
+    T_used = rm.shape[0]
+    assert torch.equal(eps.dev.observations[rows], tm.obs[:T_used][valid])
+    assert torch.equal(eps.dev.rewards[rows], tm.rew[:T_used][valid])
+    assert torch.equal(eps.dev.step_types[rows], tm.step_type[:T_used][valid])
