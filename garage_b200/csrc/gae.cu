@@ -4,6 +4,7 @@
 // HBM-bound: 17 algorithmic bytes per (t,n) element when fused
 //   (r 4 + V 4 + step_type 1 read, A 4 + R 4 written).
 #include "common.cuh"
+#include <stdlib.h>
 
 // ------------------------------------------------------ time-major kernel --
 // One thread per environment column n, sequential over t (the recurrence), the
@@ -75,6 +76,158 @@ gae_time_major_kernel(const float* __restrict__ rew, const float* __restrict__ v
     }
 }
 
+// ---------------------------------------------- time-major, time-split form --
+// When N is small the kernel above has too few threads to keep HBM busy (one thread per env, the
+// bytes in flight are N * U * 9).  Here a CTA owns 32 consecutive envs and its W warps split TIME:
+// warp w holds L rows of its envs in registers (coalesced 128 B lines as before), reduces them to
+// the affine map  (ca, next_v, cr)_in -> (ca, next_v, cr)_out  of its chunk, the maps of the warps
+// above it are folded through shared memory, and a second pass over the REGISTERS (not memory)
+// writes the outputs from the true carry: 17 B per element of traffic, W x the loads in flight.
+// The result differs from the sequential kernel only by the rounding of the folded carries.
+template <int L, int MAXW, bool HAS_ST, bool HAS_ADV, bool HAS_RET>
+__global__ void __launch_bounds__(MAXW * 32)
+gae_time_split_kernel(const float* __restrict__ rew, const float* __restrict__ val,
+                      const uint8_t* __restrict__ st, const float* __restrict__ last_val,
+                      float gamma, float gl, float* __restrict__ adv, float* __restrict__ ret,
+                      int T, int64_t N) {
+    __shared__ float sA0[MAXW][32], sPA[MAXW][32], sPV[MAXW][32], sVF[MAXW][32], sCN[MAXW][32];
+    __shared__ double sB0[MAXW][32], sPR[MAXW][32];
+    __shared__ float cCa[32], cNv[32];
+    __shared__ double cCr[32];
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5, W = blockDim.x >> 5;
+    const int64_t n = (int64_t)blockIdx.x * 32 + lane;
+    const bool on = n < N;
+    const int64_t nc = on ? n : N - 1;  // lanes past N read the last column and write nothing
+    const double gamma_d = (double)gamma;
+    if (w == 0) {
+        cCa[lane] = 0.0f;
+        cNv[lane] = (on && last_val) ? last_val[n] : 0.0f;
+        cCr[lane] = 0.0;
+    }
+    __syncthreads();
+    for (int top = T; top > 0; top -= W * L) {  // super-chunks of W*L rows, from the end of time
+        const int hi = top - w * L;              // this warp's rows: [max(hi - L, 0), hi)
+        const int cnt = hi >= L ? L : (hi > 0 ? hi : 0);
+        float r[L], v[L];
+        uint8_t sb[L];
+        const int64_t i0 = (int64_t)(hi - 1) * N + nc;  // row hi-1 (only dereferenced when cnt > 0)
+        if (cnt == L) {  // full chunk: no per-row guards, pointers step back one row at a time
+            const float* pr_ = rew + i0;
+            const float* pv_ = val + i0;
+            const uint8_t* ps_ = st + i0;
+#pragma unroll
+            for (int j = 0; j < L; ++j) {
+                r[j] = __ldcs(pr_); pr_ -= N;
+                if (HAS_ADV) { v[j] = __ldcs(pv_); pv_ -= N; }
+                if (HAS_ST) { sb[j] = __ldcs(ps_); ps_ -= N; }
+            }
+        } else {
+#pragma unroll
+            for (int j = 0; j < L; ++j) {
+                r[j] = 0.0f; v[j] = 0.0f; sb[j] = 0;
+                if (j < cnt) {
+                    const int64_t i = i0 - (int64_t)j * N;
+                    r[j] = __ldcs(rew + i);
+                    if (HAS_ADV) v[j] = __ldcs(val + i);
+                    if (HAS_ST) sb[j] = __ldcs(st + i);
+                }
+            }
+        }
+        // ---- the chunk as an affine map of the incoming carry (zero carry in: a0, b0)
+        float a0 = 0.0f, nv = 0.0f, pa = 1.0f, pv = 0.0f, cn = 1.0f;
+        double b0 = 0.0, pr = 1.0;
+#pragma unroll
+        for (int j = 0; j < L; ++j) {
+            if (j < cnt) {
+                if (HAS_ST && sb[j] >= ST_TERMINAL) {
+                    a0 = 0.0f; nv = 0.0f; pa = 0.0f; pv = 0.0f; cn = 0.0f; b0 = 0.0; pr = 0.0;
+                }
+                if (HAS_ADV) {
+                    a0 = (r[j] + gamma * nv - v[j]) + gl * a0;
+                    pv = gamma * cn + gl * pv;
+                    pa = gl * pa;
+                    nv = v[j];
+                    cn = 0.0f;
+                }
+                if (HAS_RET) {
+                    b0 = (double)r[j] + gamma_d * b0;
+                    pr = gamma_d * pr;
+                }
+            }
+        }
+        sA0[w][lane] = a0; sPA[w][lane] = pa; sPV[w][lane] = pv; sVF[w][lane] = nv; sCN[w][lane] = cn;
+        sB0[w][lane] = b0; sPR[w][lane] = pr;
+        __syncthreads();
+        // ---- true carry into this chunk: fold the maps of the warps holding later rows
+        float ca = cCa[lane], next_v = cNv[lane];
+        double cr = cCr[lane];
+        for (int u = 0; u < w; ++u) {
+            const float ca2 = sA0[u][lane] + sPA[u][lane] * ca + sPV[u][lane] * next_v;
+            next_v = sVF[u][lane] + sCN[u][lane] * next_v;
+            ca = ca2;
+            cr = sB0[u][lane] + sPR[u][lane] * cr;
+        }
+        // ---- second pass over the registers: outputs
+        float* pa_ = adv + i0;
+        float* pt_ = ret + i0;
+#pragma unroll
+        for (int j = 0; j < L; ++j) {
+            if (j < cnt) {
+                if (HAS_ST && sb[j] >= ST_TERMINAL) {
+                    ca = 0.0f; cr = 0.0; next_v = 0.0f;
+                }
+                if (HAS_ADV) {
+                    const float delta = r[j] + gamma * next_v - v[j];
+                    ca = delta + gl * ca;
+                    next_v = v[j];
+                    if (on) __stcs(pa_, ca);
+                    pa_ -= N;
+                }
+                if (HAS_RET) {
+                    cr = (double)r[j] + gamma_d * cr;
+                    if (on) __stcs(pt_, (float)cr);
+                    pt_ -= N;
+                }
+            }
+        }
+        __syncthreads();  // every warp has read the maps and the super-chunk carry
+        if (w == W - 1) { cCa[lane] = ca; cNv[lane] = next_v; cCr[lane] = cr; }
+        __syncthreads();
+    }
+}
+
+template <int L, int MAXW>
+static int launch_time_split(const float* rew, const float* val, const uint8_t* st,
+                             const float* last_val, float gamma, float lam, float* adv,
+                             float* ret, int T, int64_t N, cudaStream_t s) {
+    int W = (T + L - 1) / L;
+    if (W > MAXW) W = MAXW;
+    const unsigned blocks = (unsigned)((N + 31) / 32);
+    const float gl = gamma * lam;
+#define B2G_GAE_LAUNCH(ST, A, R)                                                                   \
+    gae_time_split_kernel<L, MAXW, ST, A, R><<<blocks, W * 32, 0, s>>>(rew, val, st, last_val, gamma, \
+                                                                      gl, adv, ret, T, N)
+    const bool hs = st != nullptr, ha = adv != nullptr, hr = ret != nullptr;
+    if (hs && ha && hr) B2G_GAE_LAUNCH(true, true, true);
+    else if (hs && ha && !hr) B2G_GAE_LAUNCH(true, true, false);
+    else if (hs && !ha && hr) B2G_GAE_LAUNCH(true, false, true);
+    else if (!hs && ha && hr) B2G_GAE_LAUNCH(false, true, true);
+    else if (!hs && ha && !hr) B2G_GAE_LAUNCH(false, true, false);
+    else B2G_GAE_LAUNCH(false, false, true);
+#undef B2G_GAE_LAUNCH
+    B2G_CHECK_LAUNCH();
+    return B2G_OK;
+}
+
+static bool gae_split_enabled() {
+    static int on = -1;
+    if (on < 0) {
+        const char* e = getenv("B2G_GAE_SPLIT");
+        on = (e && e[0] == '0') ? 0 : 1;
+    }
+    return on != 0;
+}
+
 template <int U>
 static int launch_time_major(const float* rew, const float* val, const uint8_t* st,
                              const float* last_val, float gamma, float lam, float* adv,
@@ -107,6 +260,11 @@ extern "C" int b2g_gae_time_major(const float* rew, const float* val,
     B2G_CHECK_ARG(!adv_out || val != nullptr || T * N == 0, "val is NULL but adv_out given");
     if (T == 0 || N == 0) return B2G_OK;
     cudaStream_t s = (cudaStream_t)stream;
+    // few envs, long enough in time: split time over the warps of a CTA (env B2G_GAE_SPLIT=0 turns it off)
+    if (T >= 64 && gae_split_enabled()) {
+        if (N <= 4096) return launch_time_split<32, 16>(rew, val, step_type, last_val, gamma, lam, adv_out, ret_out, T, N, s);
+        if (N < (1 << 15)) return launch_time_split<16, 8>(rew, val, step_type, last_val, gamma, lam, adv_out, ret_out, T, N, s);
+    }
     // bytes in flight ~ N * U * 9: aim for >= ~6 MB (HBM latency x bandwidth)
     if (N >= (1 << 17)) return launch_time_major<4>(rew, val, step_type, last_val, gamma, lam, adv_out, ret_out, T, N, s);
     if (N >= (1 << 16)) return launch_time_major<8>(rew, val, step_type, last_val, gamma, lam, adv_out, ret_out, T, N, s);

@@ -503,9 +503,13 @@ struct Cta {
                 __syncwarp();
             }
             stamp(5 + 10 * it);
-            if (tid >= R && tid < 2 * R) {  // row ids of the tile after next, off the critical path
+            // Row ids of the tile after next, off the critical path.  Warps 4 and 5 write them, warps 0
+            // and 1 read them in publish_rows() at the end of EPI1: the only barrier in between is the
+            // pair barrier of EPI1, which joins exactly warps (0, 4) and (1, 5) -- entry i is written by
+            // thread 2R + i and read by thread i.
+            if (tid >= 2 * R && tid < 3 * R) {
                 const int64_t t2 = tile + 2 * stride;
-                sNext[tid - R] = t2 < ntiles ? mb_src(a, t2 * R + (tid - R)) : -1;
+                sNext[tid - 2 * R] = t2 < ntiles ? mb_src(a, t2 * R + (tid - 2 * R)) : -1;
             }
             mbar_wait(bar1, par);
             tc_after_sync();
