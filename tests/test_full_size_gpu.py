@@ -149,3 +149,24 @@ def test_cartpole_16384_envs_ragged_bookkeeping_full_size():
     assert torch.equal(eps.dev.observations[rows], tm.obs[:T_used][valid])
     assert torch.equal(eps.dev.rewards[rows], tm.rew[:T_used][valid])
     assert torch.equal(eps.dev.step_types[rows], tm.step_type[:T_used][valid])
+
+
+def test_graphed_iterations_are_bit_reproducible_full_size():
+    """Two identically seeded runners replayed in lockstep must agree bit for bit after every iteration
+    (rollout buffers, packed batch, both parameter vectors).  Back-to-back graph replays are where a
+    missing barrier inside the persistent loop kernel showed up as a run-to-run difference."""
+    from garage_b200.torch.algos.graphed import GraphedIteration
+    for trial in range(4):
+        runs = []
+        for _ in range(2):
+            algo, policy, vf, sampler = _build()
+            runs.append((policy, vf, GraphedIteration(algo, N * T, warmup=1)))
+        for i in range(3):
+            for r in runs:
+                r[2].run(i)
+            torch.cuda.synchronize()
+            a, b = runs
+            assert torch.equal(a[2].eps.tm.act, b[2].eps.tm.act), (trial, i)
+            assert torch.equal(a[2].eps.dev.observations, b[2].eps.dev.observations), (trial, i)
+            assert torch.equal(a[0].flat, b[0].flat), (trial, i)
+            assert torch.equal(a[1].flat, b[1].flat), (trial, i)
