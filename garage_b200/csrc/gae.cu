@@ -263,7 +263,12 @@ extern "C" int b2g_gae_time_major(const float* rew, const float* val,
     // few envs, long enough in time: split time over the warps of a CTA (env B2G_GAE_SPLIT=0 turns it off)
     if (T >= 64 && gae_split_enabled()) {
         if (N <= 4096) return launch_time_split<32, 16>(rew, val, step_type, last_val, gamma, lam, adv_out, ret_out, T, N, s);
-        if (N < (1 << 15)) return launch_time_split<16, 8>(rew, val, step_type, last_val, gamma, lam, adv_out, ret_out, T, N, s);
+        static int64_t split_n = -1;
+        if (split_n < 0) {
+            const char* e = getenv("B2G_GAE_SPLIT_N");
+            split_n = e ? atoll(e) : (1 << 15);
+        }
+        if (N < split_n) return launch_time_split<16, 8>(rew, val, step_type, last_val, gamma, lam, adv_out, ret_out, T, N, s);
     }
     // bytes in flight ~ N * U * 9: aim for >= ~6 MB (HBM latency x bandwidth)
     if (N >= (1 << 17)) return launch_time_major<4>(rew, val, step_type, last_val, gamma, lam, adv_out, ret_out, T, N, s);
