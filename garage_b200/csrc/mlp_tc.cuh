@@ -368,6 +368,7 @@ struct Cta {
         for (int i = tid; i < A * H; i += NT) sW3[i] = ld(params + L.off_w3() + i);
         if (tid < A) sB3[tid] = ld(params + L.off_b3() + tid);
         dist = mlp_dist(a, ld(params + L.off_logstd()));
+        mlp_dist_entropy<A>(a, dist);
         fence_async_smem();
         __syncthreads();
     }
@@ -451,6 +452,8 @@ struct Cta {
     // publish the rows of tile t+1 and evaluate its first layer into registers; the rows of t+2 are in
     // flight and the ids of t+3.. are computed while GEMM1 runs.  Per tile only the panel stores, the
     // two epilogues and the MMAs themselves remain on the critical path.
+    // STATS = false: the logging sums of the loss are not accumulated (the training loop).
+    template <bool STATS = true>
     __device__ __forceinline__ void run_tiles(const MlpArgs& a, int64_t tile0, int64_t stride) {
         const int64_t ntiles = (a.mb + R - 1) / R;
         const uint32_t tfrag = tmem + ((uint32_t)(32 * q4) << 16) + TM_D + c0;
@@ -579,7 +582,7 @@ struct Cta {
 #pragma unroll
                         for (int q = 0; q < A; ++q) { in.act[q] = rin[q]; in.old_mean[q] = 0.0f; }
                         in.adv = rin[A]; in.old_logp = rin[A + 1]; in.ret = rin[A + 2];
-                        mlp_row_loss<A>(a, in, mu, dist, dm, racc);
+                        mlp_row_loss<A, STATS, true>(a, in, mu, dist, dm, racc);
                     }
 #pragma unroll
                     for (int q = 0; q < A; ++q) {
@@ -908,7 +911,7 @@ struct Cta {
                     in.old_mean[q] = om[q];
                 }
                 in.adv = sIn[er * NIN + A]; in.old_logp = sIn[er * NIN + A + 1]; in.ret = sIn[er * NIN + A + 2];
-                mlp_row_loss<A>(a, in, mu, dist, dm, racc);
+                mlp_row_loss<A, true, true>(a, in, mu, dist, dm, racc);
                 if (a.mean_out) {
 #pragma unroll
                     for (int q = 0; q < A; ++q) a.mean_out[(m0 + er) * A + q] = mu[q];

@@ -55,6 +55,9 @@ struct MlpArgs {
 struct MlpDist {  // the (state-independent) scale of the Gaussian head, gaussian_mlp_module.py:171-176
     float stdv, var, log_scale;
     bool ls_pass;  // clamp backward mask
+    // row-invariant pieces of the loss, evaluated once per weight load
+    float inv_var, inv_2var;  // 1/var, 1/(2 var): the per-row divisions become multiplications
+    float ent, dent_dls;      // entropy of Independent(Normal) (after the optional softplus) and d/d log_std
 };
 struct MlpRowAcc {  // row-owned sums: d loss / d log_std and the logging statistics
     float gLs, st_loss, st_kl, st_ent, st_clip, st_rows;
@@ -67,7 +70,25 @@ __device__ __forceinline__ MlpDist mlp_dist(const MlpArgs& a, float raw_ls) {
     d.stdv = expf(log_std);
     d.var = d.stdv * d.stdv;
     d.log_scale = logf(d.stdv);
+    d.inv_var = 1.0f / d.var;
+    d.inv_2var = 1.0f / (2.0f * d.var);
+    d.ent = 0.0f;
+    d.dent_dls = 0.0f;
     return d;
+}
+// entropy terms for an action dimension A (sum_a 0.5 + 0.5 log(2 pi) + log(std); F.softplus of it when
+// use_softplus_entropy, vpg.py:429-430)
+template <int A>
+__device__ __forceinline__ void mlp_dist_entropy(const MlpArgs& a, MlpDist& d) {
+    float ent = (float)A * (1.4189385332046727f + d.log_scale);
+    float dent_dls = (float)A;
+    if (a.flags & FLAG_SOFTPLUS_ENT) {
+        const float sp = (ent > 20.0f) ? ent : log1pf(expf(ent));
+        dent_dls *= (ent > 20.0f) ? 1.0f : 1.0f / (1.0f + expf(-ent));
+        ent = sp;
+    }
+    d.ent = ent;
+    d.dent_dls = dent_dls;
 }
 
 // per-row inputs of the loss (gathered at the minibatch row id)
@@ -96,43 +117,45 @@ __device__ __forceinline__ MlpRowIn<A> mlp_row_in(const MlpArgs& a, int64_t src)
     return in;
 }
 
-// loss of one valid row given the network output mu: writes dmu (x 1/mb later), accumulates acc
-template <int A>
+// loss of one valid row given the network output mu: writes dmu (x 1/mb later), accumulates acc.
+// STATS = false drops the logging sums (the fused training loop does not report them);
+// FAST uses ex2.approx for the probability ratio (2 ulp; the tensor-core paths).
+template <int A, bool STATS = true, bool FAST = false>
 __device__ __forceinline__ void mlp_row_loss(const MlpArgs& a, const MlpRowIn<A>& in, const float (&mu)[A],
                                              const MlpDist& ds, float (&dmu)[A], MlpRowAcc& acc) {
-    const float var = ds.var, stdv = ds.stdv, log_scale = ds.log_scale;
+    const float stdv = ds.stdv, log_scale = ds.log_scale, inv_var = ds.inv_var;
     const bool ls_pass = ds.ls_pass;
-    acc.st_rows += 1.0f;
-    // entropy of Independent(Normal): sum_a 0.5 + 0.5 log(2 pi) + log(std)
-    float ent = (float)A * (1.4189385332046727f + log_scale);
-    float dent_dls = (float)A;  // d entropy / d log_std
-    if (a.flags & FLAG_SOFTPLUS_ENT) {  // F.softplus(entropy), vpg.py:429-430
-        const float sp = (ent > 20.0f) ? ent : log1pf(expf(ent));
-        dent_dls *= (ent > 20.0f) ? 1.0f : 1.0f / (1.0f + expf(-ent));
-        ent = sp;
+    const float ent = ds.ent, dent_dls = ds.dent_dls;  // mlp_dist_entropy<A>() ran after mlp_dist()
+    if (STATS) {
+        acc.st_rows += 1.0f;
+        acc.st_ent += ent;
     }
-    acc.st_ent += ent;
     if (a.loss_kind == LOSS_NONE) {
         // forward only (baselines / means)
     } else if (a.loss_kind == LOSS_VF) {
         // -log N(ret; mu, std): gaussian_mlp_value_function.py:81-97
         const float d = in.ret - mu[0];
-        acc.st_loss += (d * d) / (2.0f * var) + log_scale + 0.9189385332046727f;
-        dmu[0] = -d / var;                               // d loss / d mu (x 1/mb later)
-        if (ls_pass) acc.gLs += 1.0f - (d * d) / var;    // d loss / d log_std
+        if (STATS) acc.st_loss += (d * d) * ds.inv_2var + log_scale + 0.9189385332046727f;
+        dmu[0] = -d * inv_var;                                  // d loss / d mu (x 1/mb later)
+        if (ls_pass) acc.gLs += 1.0f - (d * d) * inv_var;       // d loss / d log_std
     } else {
         float ll = 0.0f, dsq = 0.0f, dact[A];
 #pragma unroll
         for (int q = 0; q < A; ++q) {
-            const float av = in.act[q];
-            ll += normal_logp_term(av, mu[q], var, log_scale);
-            dact[q] = av - mu[q];
+            dact[q] = in.act[q] - mu[q];
             dsq += dact[q] * dact[q];
         }
+        // Independent(Normal).log_prob: sum_a -(a - mu)^2 / (2 var) - log(std) - log(sqrt(2 pi))
+        ll = -dsq * ds.inv_2var - (float)A * (log_scale + 0.9189385332046727f);
         const float adv = in.adv;
         float obj, dobj_dll;
         if (a.loss_kind == LOSS_PPO) {  // ppo.py:113-132
-            const float ratio = expf(ll - in.old_logp);
+            float ratio;
+            if (FAST) {
+                asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(ratio) : "f"((ll - in.old_logp) * 1.4426950408889634f));
+            } else {
+                ratio = expf(ll - in.old_logp);
+            }
             const float lo = 1.0f - a.clip, hi = 1.0f + a.clip;
             const float rc = fminf(fmaxf(ratio, lo), hi);
             const float surr = ratio * adv, surr_c = rc * adv;
@@ -141,7 +164,7 @@ __device__ __forceinline__ void mlp_row_loss(const MlpArgs& a, const MlpRowIn<A>
             // torch.min ties split the gradient, clamp passes it inside [lo,hi]
             const bool pass = inside || (surr < surr_c);
             dobj_dll = pass ? ratio * adv : 0.0f;
-            if (!inside) acc.st_clip += 1.0f;
+            if (STATS && !inside) acc.st_clip += 1.0f;
         } else {  // vpg.py:452-455
             obj = ll * adv;
             dobj_dll = adv;
@@ -151,11 +174,12 @@ __device__ __forceinline__ void mlp_row_loss(const MlpArgs& a, const MlpRowIn<A>
             obj += a.ent_coeff * ent;
             if (!(a.flags & FLAG_STOP_ENT_GRAD)) dobj_dls = a.ent_coeff * dent_dls;
         }
-        acc.st_loss -= obj;
+        if (STATS) acc.st_loss -= obj;
+        const float s = -dobj_dll * inv_var;
 #pragma unroll
-        for (int q = 0; q < A; ++q) dmu[q] = -dobj_dll * dact[q] / var;
-        if (ls_pass) acc.gLs -= dobj_dll * (dsq / var - (float)A) + dobj_dls;
-        if (a.old_mean) {  // torch kl_normal_normal(old, new), vpg.py:381-406
+        for (int q = 0; q < A; ++q) dmu[q] = s * dact[q];
+        if (ls_pass) acc.gLs -= dobj_dll * (dsq * inv_var - (float)A) + dobj_dls;
+        if (STATS && a.old_mean) {  // torch kl_normal_normal(old, new), vpg.py:381-406
             const float so = expf(a.old_log_std ? __ldg(a.old_log_std) : 0.0f);
             const float vr = (so / stdv) * (so / stdv);
 #pragma unroll
@@ -216,7 +240,8 @@ __global__ void __launch_bounds__(MLP_NT, 2) mlp_train_kernel(const MlpArgs a) {
     }
     for (int i = tid; i < A * H; i += MLP_NT) sW3[i] = a.params[L.off_w3() + i];
     if (tid < A) sB3[tid] = a.params[L.off_b3() + tid];
-    const MlpDist dist = mlp_dist(a, a.params[L.off_logstd()]);
+    MlpDist dist = mlp_dist(a, a.params[L.off_logstd()]);
+    mlp_dist_entropy<A>(a, dist);
     if (BWD && a.step_counter && blockIdx.x == 0 && tid == 0) *a.step_counter += 1ull;
     __syncthreads();
 

@@ -170,7 +170,7 @@ __device__ __forceinline__ void net_loop(const NetLoop& n, int j, int ctas, uint
             LOOP_STAMP(0);
             cta.stamps = (n.timing && gstep == n.timing_step) ? n.tile_timing + (int64_t)j * 32 : nullptr;
             cta.stamp(0);
-            cta.run_tiles(a, j, ctas);
+            cta.template run_tiles<false>(a, j, ctas);
             cta.stamps = nullptr;
         }
         LOOP_STAMP(1);
