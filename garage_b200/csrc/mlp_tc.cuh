@@ -346,28 +346,42 @@ struct Cta {
     template <class Ld>
     __device__ __forceinline__ void load_weights(const MlpArgs& a, const float* params, Ld ld) {
         const MlpLayout L{O, H, A};
+        // All CTAs read the same 18 KB right after the update: the loads are fully coalesced (a warp reads
+        // 128 contiguous bytes; W2 starts at a 4-byte aligned offset, so no vector loads) and all issued
+        // before the first shared-memory store (a load behind a store through a generic pointer would
+        // wait for it: one L2 round trip per group instead of one in total).
+        static_assert(H * O <= NT && A * H <= NT && 2 * H <= NT && H * H == 16 * NT, "thread <-> parameter mapping");
+        const float* w2 = params + L.off_w2();
+        float v[16];
+#pragma unroll
+        for (int i = 0; i < 16; ++i) v[i] = ld(w2 + tid + NT * i);
+        const float w1v = tid < H * O ? ld(params + L.off_w1() + tid) : 0.0f;
+        const float bv = tid < H ? ld(params + L.off_b1() + tid) : (tid < 2 * H ? ld(params + L.off_b2() + tid - H) : 0.0f);
+        const float w3v = tid < A * H ? ld(params + L.off_w3() + tid) : 0.0f;
+        const float b3v = tid < A ? ld(params + L.off_b3() + tid) : 0.0f;
+        const float lsv = ld(params + L.off_logstd());
         {
-            const float* w2 = params + L.off_w2();  // 4-byte aligned only (offset 1 + H*O + H floats)
-            float v[4][4];
+            // element e = tid + 256 i of W2[c][k]: k = e & 63 does not depend on i; a warp writes one
+            // 128-byte panel row (32 banks)
+            const int k = tid & 63;
+            uint8_t* hi_p = smem + OFF_W + (uint32_t)(k >> 5) * WPANEL + (k & 3) * 4;
+            uint8_t* lo_p = hi_p + 2 * WPANEL;
 #pragma unroll
-            for (int i = 0; i < 4; ++i)
-#pragma unroll
-                for (int j = 0; j < 4; ++j) v[i][j] = ld(w2 + (tid + NT * i) * 4 + j);
-#pragma unroll
-            for (int i = 0; i < 4; ++i) {
-                const int e = (tid + NT * i) * 4, c = e >> 6, k = e & 63;
-                const uint32_t off = (uint32_t)(k >> 5) * WPANEL + chunk_off(c, (k & 31) >> 2);
-                store_split4(smem + OFF_W, smem + OFF_W + 2 * WPANEL, off, v[i]);
+            for (int i = 0; i < 16; ++i) {
+                const int c = (tid >> 6) + 4 * i;
+                const uint32_t off = chunk_off(c, (k & 31) >> 2);
+                float h, l2;
+                split_tf32(v[i], h, l2);
+                *reinterpret_cast<float*>(hi_p + off) = h;
+                *reinterpret_cast<float*>(lo_p + off) = l2;
             }
         }
-        for (int i = tid; i < H * O; i += NT) sW1[i] = ld(params + L.off_w1() + i);
-        if (tid < H) {
-            sB1[tid] = ld(params + L.off_b1() + tid);
-            sB2[tid] = ld(params + L.off_b2() + tid);
-        }
-        for (int i = tid; i < A * H; i += NT) sW3[i] = ld(params + L.off_w3() + i);
-        if (tid < A) sB3[tid] = ld(params + L.off_b3() + tid);
-        dist = mlp_dist(a, ld(params + L.off_logstd()));
+        if (tid < H * O) sW1[tid] = w1v;
+        if (tid < H) sB1[tid] = bv;
+        else if (tid < 2 * H) sB2[tid - H] = bv;
+        if (tid < A * H) sW3[tid] = w3v;
+        if (tid < A) sB3[tid] = b3v;
+        dist = mlp_dist(a, lsv);
         mlp_dist_entropy<A>(a, dist);
         fence_async_smem();
         __syncthreads();
