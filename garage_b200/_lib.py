@@ -38,6 +38,14 @@ class TrainComm(ctypes.Structure):
     _fields_ = [('world', c_int), ('rank', c_int), ('peer_base', P * MAX_RANKS)]
 
 
+class Norm(ctypes.Structure):
+    """`b2g_norm` of include/b2g.h (the normalize(env) wrapper fused into the step)."""
+    _fields_ = [('flags', c_int), ('act_low', c_float * 2), ('act_high', c_float * 2),
+                ('expected_action_scale', c_float),
+                ('scale_reward', c_double), ('obs_alpha', c_double), ('reward_alpha', c_double),
+                ('stats', P)]
+
+
 # name -> (restype, argtypes); mirrors include/b2g.h one to one
 SIGNATURES = {
     'b2g_version': (c_int, []),
@@ -60,6 +68,11 @@ SIGNATURES = {
     'b2g_rollout': (c_int, [c_int, POINTER(c_double), c_int, P, c_int, c_float, c_float, c_uint64,
                             c_int64, c_uint32, P, P, P, P, P, c_int, c_int64, P, P, P, P, P, P, P, P,
                             P, P]),
+    'b2g_env_reset_norm': (c_int, [c_int, POINTER(c_double), POINTER(Norm), c_uint64, c_int64, P, P, P, P, c_int64, P]),
+    'b2g_env_step_norm': (c_int, [c_int, POINTER(c_double), POINTER(Norm), c_int, P, P, P, P, P, P, P, P, c_int64, P]),
+    'b2g_rollout_norm': (c_int, [c_int, POINTER(c_double), POINTER(Norm), c_int, P, c_int, c_float, c_float,
+                                 c_uint64, c_int64, c_uint32, P, P, P, P, P, c_int, c_int64, P, P, P, P, P, P,
+                                 P, P, P, P]),
     'b2g_policy_sample': (c_int, [P, c_int, c_float, c_uint64, c_int64, c_uint32, P, P, c_int64, P]),
     'b2g_pack_ws_bytes': (c_int64, [c_int]),
     'b2g_pack_plan': (c_int, [P, P, c_int, c_int64, c_int64, P, P, P]),

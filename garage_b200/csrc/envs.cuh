@@ -143,3 +143,87 @@ __device__ __forceinline__ StepOut env_step(const EnvParams& P, double* s, const
     }
     return o;
 }
+
+// ------------------------------------------------------- normalize(env) --
+// envs/normalized_env.py:8-171 as a prologue / epilogue of env_step and env_reset (see b2g.h).
+struct NormParams {
+    int flags;
+    float lo[2], hi[2], es;
+    double scale_reward, oa, ra;
+    double* stats;  // [2*O + 2, N]
+};
+
+inline bool norm_from_host(const b2g_norm* h, NormParams* q) {
+    *q = NormParams{};
+    q->scale_reward = 1.0;
+    if (!h) return true;
+    if ((h->flags & (B2G_NORM_OBS | B2G_NORM_REWARD)) && !h->stats) return false;
+    q->flags = h->flags;
+    for (int i = 0; i < 2; ++i) { q->lo[i] = h->act_low[i]; q->hi[i] = h->act_high[i]; }
+    q->es = h->expected_action_scale;
+    q->scale_reward = h->scale_reward; q->oa = h->obs_alpha; q->ra = h->reward_alpha;
+    q->stats = h->stats;
+    return true;
+}
+inline bool norm_active(const NormParams& q) { return q.flags != 0 || q.scale_reward != 1.0; }
+
+template <int O>
+struct NormStats {
+    double om[O], ov[O], rm, rv;
+    __device__ __forceinline__ void load(const NormParams& q, int64_t N, int64_t n) {
+        if (q.flags & (B2G_NORM_OBS | B2G_NORM_REWARD)) {
+#pragma unroll
+            for (int i = 0; i < O; ++i) { om[i] = q.stats[(int64_t)i * N + n]; ov[i] = q.stats[(int64_t)(O + i) * N + n]; }
+            rm = q.stats[(int64_t)(2 * O) * N + n];
+            rv = q.stats[(int64_t)(2 * O + 1) * N + n];
+        }
+    }
+    __device__ __forceinline__ void store(const NormParams& q, int64_t N, int64_t n) const {
+        if (q.flags & B2G_NORM_OBS) {
+#pragma unroll
+            for (int i = 0; i < O; ++i) { q.stats[(int64_t)i * N + n] = om[i]; q.stats[(int64_t)(O + i) * N + n] = ov[i]; }
+        }
+        if (q.flags & B2G_NORM_REWARD) {
+            q.stats[(int64_t)(2 * O) * N + n] = rm;
+            q.stats[(int64_t)(2 * O + 1) * N + n] = rv;
+        }
+    }
+    // _apply_normalize_obs (:133-146): update the estimate, then normalise with the NEW estimate.
+    // Separate multiplies and adds (numpy evaluates them one by one: no fused multiply-add).
+    __device__ __forceinline__ void obs(const NormParams& q, float* ob) {
+        if (!(q.flags & B2G_NORM_OBS)) return;
+#pragma unroll
+        for (int i = 0; i < O; ++i) {
+            const double o = (double)ob[i];
+            om[i] = __dadd_rn(__dmul_rn(1.0 - q.oa, om[i]), __dmul_rn(q.oa, o));
+            const double d = o - om[i];
+            ov[i] = __dadd_rn(__dmul_rn(1.0 - q.oa, ov[i]), __dmul_rn(q.oa, __dmul_rn(d, d)));
+            ob[i] = (float)(d / (sqrt(ov[i]) + 1e-8));
+        }
+    }
+    // _apply_normalize_reward (:148-160) and scale_reward (:112)
+    __device__ __forceinline__ double reward(const NormParams& q, double r) {
+        if (q.flags & B2G_NORM_REWARD) {
+            rm = __dadd_rn(__dmul_rn(1.0 - q.ra, rm), __dmul_rn(q.ra, r));
+            const double d = r - rm;
+            rv = __dadd_rn(__dmul_rn(1.0 - q.ra, rv), __dmul_rn(q.ra, __dmul_rn(d, d)));
+            r = r / (sqrt(rv) + 1e-8);
+        }
+        return r * q.scale_reward;
+    }
+};
+
+// step():91-101 -- the action the wrapped env receives
+template <int A>
+__device__ __forceinline__ void norm_action(const NormParams& q, const float* act, float* scaled) {
+#pragma unroll
+    for (int i = 0; i < A; ++i) {
+        float v = act[i];
+        if (q.flags & B2G_NORM_ACTION) {
+            const float k = __fdiv_rn(__fmul_rn(0.5f, __fsub_rn(q.hi[i], q.lo[i])), q.es);
+            v = __fadd_rn(q.lo[i], __fmul_rn(__fadd_rn(v, q.es), k));
+            v = fminf(fmaxf(v, q.lo[i]), q.hi[i]);
+        }
+        scaled[i] = v;
+    }
+}

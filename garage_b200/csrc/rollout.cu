@@ -17,6 +17,7 @@
 
 struct RolloutArgs {
     EnvParams P;
+    NormParams Q;        // normalize(env) wrapper (envs.cuh); used by the NORM instantiations only
     uint32_t seed_lo, seed_hi;
     int64_t gid0;
     uint32_t t_counter;  // global step counter of row 0 (Philox counter word)
@@ -42,7 +43,7 @@ struct RolloutArgs {
 
 constexpr int RO_WARPS = 4;
 
-template <int ENV, int H, int G>
+template <int ENV, int H, int G, bool NORM>
 __global__ void __launch_bounds__(RO_WARPS * 32)
 rollout_kernel(const RolloutArgs a) {
     constexpr int O = EnvDims<ENV>::O, A = EnvDims<ENV>::A, S = EnvDims<ENV>::S;
@@ -93,6 +94,8 @@ rollout_kernel(const RolloutArgs a) {
     double s[S];
     float ob[O];
     int cnt = 0, ep = 0;
+    NormStats<NORM ? O : 1> ns;
+    if (NORM && owner) ns.load(a.Q, N, n);
     if (owner) {
 #pragma unroll
         for (int i = 0; i < S; ++i) s[i] = a.state[(int64_t)i * N + n];
@@ -189,7 +192,16 @@ rollout_kernel(const RolloutArgs a) {
                 for (int q = 0; q < A; ++q) a.mean[row * A + q] = mu[q];
             }
             a.logp[row] = lp;
-            const StepOut r = env_step<ENV>(a.P, s, act, ob);
+            StepOut r;
+            if constexpr (NORM) {  // normalized_env.py:75-115
+                float sa[A];
+                norm_action<A>(a.Q, act, sa);
+                r = env_step<ENV>(a.P, s, sa, ob);
+                ns.obs(a.Q, ob);
+                r.reward = ns.reward(a.Q, r.reward);
+            } else {
+                r = env_step<ENV>(a.P, s, act, ob);
+            }
             cnt += 1;
             const uint8_t st = b2g_step_type(cnt, a.P.max_len, r.done);
             a.rew[row] = (float)r.reward;
@@ -203,6 +215,7 @@ rollout_kernel(const RolloutArgs a) {
                 }
                 // vec_worker.py:171: the finished env is reset immediately
                 env_reset<ENV>(a.P, a.seed_lo, a.seed_hi, gid, (uint32_t)ep, s, ob);
+                if constexpr (NORM) ns.obs(a.Q, ob);  // reset() normalises too (:71-73)
                 ep += 1;
                 cnt = 0;
             }
@@ -215,6 +228,7 @@ rollout_kernel(const RolloutArgs a) {
         for (int i = 0; i < O; ++i) a.cur_obs[n * O + i] = ob[i];
         a.step_cnt[n] = cnt;
         a.episode[n] = ep;
+        if constexpr (NORM) ns.store(a.Q, N, n);
     }
 }
 
@@ -231,7 +245,8 @@ static int launch_rollout(const RolloutArgs& a, cudaStream_t s) {
     {                                                                                \
         const int64_t warps = (a.N + GG - 1) / GG;                                   \
         const unsigned blocks = (unsigned)((warps + RO_WARPS - 1) / RO_WARPS);       \
-        rollout_kernel<ENV, H, GG><<<blocks, RO_WARPS * 32, 0, s>>>(a);              \
+        if (norm_active(a.Q)) rollout_kernel<ENV, H, GG, true><<<blocks, RO_WARPS * 32, 0, s>>>(a);  \
+        else rollout_kernel<ENV, H, GG, false><<<blocks, RO_WARPS * 32, 0, s>>>(a);  \
     }
     switch (G) {
         case 1: B2G_RO(1); break;
@@ -253,8 +268,24 @@ extern "C" int b2g_rollout(int env_id, const double* params, int max_episode_len
                            float* obs, float* act, float* rew, float* logp,
                            uint8_t* step_type, float* mean, uint8_t* success,
                            float* last_obs, int32_t* ep_len, void* stream) {
+    return b2g_rollout_norm(env_id, params, nullptr, max_episode_length, policy_params, hidden, min_log_std,
+                            max_log_std, seed, env_id_offset, t_counter, t_counter_dev, state, cur_obs, step_cnt,
+                            episode, n_steps, N, obs, act, rew, logp, step_type, mean, success, last_obs, ep_len,
+                            stream);
+}
+
+extern "C" int b2g_rollout_norm(int env_id, const double* params, const b2g_norm* norm, int max_episode_length,
+                                const float* policy_params, int hidden, float min_log_std,
+                                float max_log_std, uint64_t seed, int64_t env_id_offset,
+                                uint32_t t_counter, const unsigned long long* t_counter_dev,
+                                double* state, float* cur_obs,
+                                int32_t* step_cnt, int32_t* episode, int n_steps, int64_t N,
+                                float* obs, float* act, float* rew, float* logp,
+                                uint8_t* step_type, float* mean, uint8_t* success,
+                                float* last_obs, int32_t* ep_len, void* stream) {
     RolloutArgs a;
     B2G_CHECK_ARG(env_params_from_host(env_id, params, max_episode_length, &a.P), "bad env_id or params");
+    B2G_CHECK_ARG(norm_from_host(norm, &a.Q), "normalize_obs / normalize_reward need the stats buffer");
     B2G_CHECK_ARG(n_steps >= 0 && N >= 0, "negative shape");
     if (hidden != 32 && hidden != 64) {
         b2g_set_error("b2g_rollout: hidden_sizes=(%d,%d) not built (supported: (32,32), (64,64))", hidden, hidden);

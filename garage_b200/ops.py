@@ -133,25 +133,79 @@ def env_dims(env_id):
     return lib.b2g_env_obs_dim(env_id), lib.b2g_env_act_dim(env_id), lib.b2g_env_state_dim(env_id)
 
 
+NORM_ACTION, NORM_OBS, NORM_REWARD = 1, 2, 4
+
+
+class NormConfig:
+    """Host description of `normalize(env, ...)` (reference envs/normalized_env.py:29-55); the
+    per-env running statistics live in `EnvState.norm_stats`."""
+
+    def __init__(self, flags, act_low, act_high, expected_action_scale=1., scale_reward=1.,
+                 obs_alpha=0.001, reward_alpha=0.001):
+        self.flags = int(flags)
+        self.act_low = [float(v) for v in act_low]
+        self.act_high = [float(v) for v in act_high]
+        self.expected_action_scale = float(expected_action_scale)
+        self.scale_reward = float(scale_reward)
+        self.obs_alpha, self.reward_alpha = float(obs_alpha), float(reward_alpha)
+
+    @property
+    def needs_stats(self):
+        return bool(self.flags & (NORM_OBS | NORM_REWARD))
+
+    def struct(self, es):
+        """ctypes `b2g_norm` bound to the statistics of EnvState `es` (allocated on first use)."""
+        q = _lib.Norm()
+        q.flags = self.flags
+        for i in range(2):
+            q.act_low[i] = self.act_low[i] if i < len(self.act_low) else 0.
+            q.act_high[i] = self.act_high[i] if i < len(self.act_high) else 0.
+        q.expected_action_scale = self.expected_action_scale
+        q.scale_reward, q.obs_alpha, q.reward_alpha = self.scale_reward, self.obs_alpha, self.reward_alpha
+        if self.needs_stats:
+            if es.norm_stats is None:
+                es.norm_stats = new_norm_stats(es.env_id, es.n, es.device)
+            q.stats = es.norm_stats.data_ptr()
+        else:
+            q.stats = None
+        return q
+
+
+def new_norm_stats(env_id, n, device):
+    """[2*O + 2, n] float64: obs_mean = 0, obs_var = 1, reward_mean = 0, reward_var = 1
+    (normalized_env.py:50-55)."""
+    O = env_dims(env_id)[0]
+    st = torch.zeros(2 * O + 2, n, dtype=torch.float64, device=device)
+    st[O:2 * O] = 1.
+    st[2 * O + 1] = 1.
+    return st
+
+
+def _norm_arg(es, norm):
+    return None if norm is None else ctypes.byref(norm.struct(es))
+
+
 class EnvState:
     """Device-resident state of N batched environments (caller-owned tensors)."""
 
     def __init__(self, env_id, n, device):
         O, A, S = env_dims(env_id)
         self.env_id, self.n, self.device = env_id, n, device
+        self.norm_stats = None  # running statistics of normalize(env), see NormConfig
         self.state = torch.zeros(S, n, dtype=torch.float64, device=device)
         self.obs = torch.zeros(n, O, dtype=torch.float32, device=device)
         self.step_cnt = torch.full((n, ), -1, dtype=torch.int32, device=device)
         self.episode = torch.zeros(n, dtype=torch.int32, device=device)
 
 
-def env_reset(es, params, seed, env_id_offset=0):
+def env_reset(es, params, seed, env_id_offset=0, norm=None):
     with torch.cuda.device(es.device):
-        call('b2g_env_reset', es.env_id, params, int(seed) & (2**64 - 1), int(env_id_offset),
-             ptr(es.state), ptr(es.obs), ptr(es.step_cnt), ptr(es.episode), es.n, _stream(es.state))
+        call('b2g_env_reset_norm', es.env_id, params, _norm_arg(es, norm), int(seed) & (2**64 - 1),
+             int(env_id_offset), ptr(es.state), ptr(es.obs), ptr(es.step_cnt), ptr(es.episode), es.n,
+             _stream(es.state))
 
 
-def env_step(es, params, max_episode_length, actions, want_success=False):
+def env_step(es, params, max_episode_length, actions, want_success=False, norm=None):
     """One Environment.step() for all envs. Returns (obs, reward f64, step_type u8, success|None)."""
     _chk(actions, torch.float32, 'actions')
     O, A, S = env_dims(es.env_id)
@@ -164,7 +218,7 @@ def env_step(es, params, max_episode_length, actions, want_success=False):
     succ = torch.empty(es.n, dtype=torch.uint8, device=dev) if want_success else None
     err = torch.zeros(1, dtype=torch.int32, device=dev)
     with torch.cuda.device(dev):
-        call('b2g_env_step', es.env_id, params, int(max_episode_length or 0), ptr(es.state),
+        call('b2g_env_step_norm', es.env_id, params, _norm_arg(es, norm), int(max_episode_length or 0), ptr(es.state),
              ptr(actions), ptr(obs), ptr(rew), ptr(st), ptr(succ), ptr(es.step_cnt), ptr(err),
              es.n, _stream(actions))
     bad = int(err.item())
@@ -204,7 +258,7 @@ def counter_add(counter, delta):
 
 
 def rollout(es, params, max_episode_length, policy_flat, hidden, min_log_std, max_log_std, seed,
-            env_id_offset, t_counter, buf, t0, n_steps, t_counter_dev=None):
+            env_id_offset, t_counter, buf, t0, n_steps, t_counter_dev=None, norm=None):
     """b2g_rollout for rows t0..t0+n_steps of `buf`."""
     _chk(policy_flat, torch.float32, 'policy_flat')
     if t0 + n_steps > buf.T:
@@ -214,7 +268,7 @@ def rollout(es, params, max_episode_length, policy_flat, hidden, min_log_std, ma
         return None if t is None else t[t0:]
 
     with torch.cuda.device(es.device):
-        call('b2g_rollout', es.env_id, params, int(max_episode_length or 0), ptr(policy_flat),
+        call('b2g_rollout_norm', es.env_id, params, _norm_arg(es, norm), int(max_episode_length or 0), ptr(policy_flat),
              int(hidden), float(min_log_std), float(max_log_std), int(seed) & (2**64 - 1),
              int(env_id_offset), int(t_counter) & 0xffffffff, ptr(t_counter_dev), ptr(es.state), ptr(es.obs),
              ptr(es.step_cnt), ptr(es.episode), int(n_steps), es.n, ptr(row(buf.obs)),

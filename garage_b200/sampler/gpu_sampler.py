@@ -160,8 +160,11 @@ class GPUSampler(Sampler):
         self._ensure_state()
         prm = env.params_array()
         pol = self._policy
+        # normalize(env): the wrapper's arithmetic runs inside the kernels; its running estimates
+        # stay in self._es.norm_stats across calls, as each worker's env copy keeps them
+        norm = env.norm_config() if hasattr(env, 'norm_config') else None
         # update_agent -> every env restarts from reset() (vec_worker.py:107-137)
-        ops.env_reset(self._es, prm, self._seed, self._env_id_offset)
+        ops.env_reset(self._es, prm, self._seed, self._env_id_offset, norm=norm)
         static = bool(getattr(env, 'never_terminates', False)) and L > 0
         if static:
             rows = int(math.ceil(num_samples / float(N * L))) * L
@@ -175,7 +178,7 @@ class GPUSampler(Sampler):
         while True:
             ops.rollout(self._es, prm, L, pol.flat, pol.mlp_shape.H, pol._module.min_log_std,
                         pol._module.max_log_std, self._seed, self._env_id_offset, 0,
-                        self._buf, done_rows, rows - done_rows, t_counter_dev=self._t_dev)
+                        self._buf, done_rows, rows - done_rows, t_counter_dev=self._t_dev, norm=norm)
             ops.counter_add(self._t_dev, rows - done_rows)
             done_rows = rows
             if static:

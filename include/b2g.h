@@ -185,6 +185,49 @@ int b2g_rollout(int env_id, const double* params, int max_episode_length,
                 float* obs, float* act, float* rew, float* logp, uint8_t* step_type,
                 float* mean, uint8_t* success, float* last_obs, int32_t* ep_len, void* stream);
 
+/* ------------------------------------------------------ normalize(env) --
+ * envs/normalized_env.py:8-171 (`normalize = NormalizedEnv`), the wrapper garage's
+ * benchmark launchers put around every env
+ * (benchmarks/.../algos/ppo_garage_pytorch.py:36), fused into the step:
+ *   B2G_NORM_ACTION  :91-101  scaled = clip(lb + (a + s) * (0.5 (ub - lb) / s), lb, ub) in
+ *                    float32 like numpy on the float32 action; the host sets the flag from the
+ *                    reference's bound test (:94, including its `ub != -inf` spelling).  The
+ *                    stored action stays the UNSCALED one (:111).
+ *   B2G_NORM_OBS     :117-146  per env copy: mean = (1-a) mean + a o; var = (1-a) var + a (o - mean)^2
+ *                    (the NEW mean); o' = (o - mean) / (sqrt(var) + 1e-8); float64.  Applied to the
+ *                    observation of reset() (:71-73) and of every step (:106-107).
+ *   B2G_NORM_REWARD  :124-131, 148-160  same recursion on the reward; r' = r / (sqrt(var) + 1e-8).
+ *   scale_reward     :112  multiplies the (normalised) reward.
+ * stats: device float64 [2*O + 2, N] SoA = obs_mean[O], obs_var[O], reward_mean, reward_var of
+ * every env copy (initially 0 / 1 / 0 / 1, :50-55); it persists across calls like the wrapper
+ * object does.  A NULL `norm` (or flags 0, scale_reward 1) is the bare environment. */
+#define B2G_NORM_ACTION 1
+#define B2G_NORM_OBS 2
+#define B2G_NORM_REWARD 4
+typedef struct b2g_norm {
+    int flags;
+    float act_low[2], act_high[2]; /* action_space.low / .high (float32) */
+    float expected_action_scale;
+    double scale_reward, obs_alpha, reward_alpha;
+    double* stats; /* device [2*O + 2, N] */
+} b2g_norm;
+
+/* b2g_env_reset / b2g_env_step / b2g_rollout with the wrapper applied (same arguments + norm). */
+int b2g_env_reset_norm(int env_id, const double* params, const b2g_norm* norm, uint64_t seed,
+                       int64_t env_id_offset, double* state, float* obs, int32_t* step_cnt,
+                       int32_t* episode, int64_t N, void* stream);
+int b2g_env_step_norm(int env_id, const double* params, const b2g_norm* norm, int max_episode_length,
+                      double* state, const float* actions, float* obs_out, double* reward_out,
+                      uint8_t* step_type_out, uint8_t* success_out, int32_t* step_cnt,
+                      int32_t* err_flag, int64_t N, void* stream);
+int b2g_rollout_norm(int env_id, const double* params, const b2g_norm* norm, int max_episode_length,
+                     const float* policy_params, int hidden, float min_log_std, float max_log_std,
+                     uint64_t seed, int64_t env_id_offset, uint32_t t_counter,
+                     const unsigned long long* t_counter_dev, double* state,
+                     float* cur_obs, int32_t* step_cnt, int32_t* episode, int n_steps, int64_t N,
+                     float* obs, float* act, float* rew, float* logp, uint8_t* step_type,
+                     float* mean, uint8_t* success, float* last_obs, int32_t* ep_len, void* stream);
+
 /* ------------------------------------------------------- EpisodeBatch pack --
  * Time-major rollout buffers -> garage's episode-major packed EpisodeBatch
  * layout; replaces sampler/vec_worker.py:139-174,206-219, the ">= num_samples,

@@ -86,6 +86,59 @@ def gen_point_env():
     np.savez_compressed(os.path.join(OUT, 'point_env.npz'), **out)
 
 
+def gen_normalized_env():
+    """`normalize(PointEnv(...), ...)` of the reference over several episodes (the wrapper's
+    running estimates persist across reset()): actions in, observations / rewards / final
+    estimates out."""
+    from garage.envs import PointEnv, normalize
+    rng = np.random.default_rng(5)
+    out = {}
+    cfgs = dict(
+        a=dict(env=dict(goal=(1., 1.), max_episode_length=20), norm=dict()),  # default: action scaling only
+        b=dict(env=dict(goal=(0.5, -0.4), max_episode_length=25),
+               norm=dict(normalize_obs=True, normalize_reward=True, scale_reward=0.5, obs_alpha=0.05,
+                         reward_alpha=0.02)),
+        c=dict(env=dict(goal=(0.3, 0.3), done_bonus=2., max_episode_length=30),
+               norm=dict(normalize_obs=True, expected_action_scale=2., obs_alpha=0.01)),
+        d=dict(env=dict(goal=(2., 2.), max_episode_length=15),
+               norm=dict(normalize_reward=True, scale_reward=3., reward_alpha=0.1)))
+    for name, c in cfgs.items():
+        kw = c['env']
+        env = normalize(PointEnv(**{k: (np.array(v, dtype=np.float32) if k == 'goal' else v) for k, v in kw.items()}),
+                        **c['norm'])
+        goal = np.array(kw['goal'], np.float32)
+        scale = c['norm'].get('expected_action_scale', 1.)
+        acts, obs, rews, sts, first = [], [], [], [], []
+        for ep in range(3):
+            o, _ = env.reset()
+            first.append(len(acts))
+            obs.append(np.asarray(o, np.float64))
+            pos = np.zeros(2)
+            for t in range(kw['max_episode_length']):
+                # in units of expected_action_scale: towards the goal, noisy, sometimes out of range
+                a = (scale * np.clip(3. * (goal - pos), -1.3, 1.3) + rng.standard_normal(2) * 0.3 * scale).astype(np.float32)
+                es = env.step(a)
+                pos = np.asarray(env._env._point, np.float64)
+                acts.append(a); obs.append(np.asarray(es.observation, np.float64)); rews.append(float(es.reward))
+                sts.append(int(es.step_type))
+                if es.last:
+                    break
+        nk = c['norm']
+        out.update({name + '_actions': np.array(acts, np.float32), name + '_obs': np.array(obs, np.float64),
+                    name + '_rewards': np.array(rews, np.float64), name + '_step_types': np.array(sts, np.uint8),
+                    name + '_first': np.array(first, np.int64),
+                    name + '_env': np.array([goal[0], goal[1], 5., kw.get('done_bonus', 0.), 0.,
+                                             kw['max_episode_length']], np.float64),
+                    name + '_norm': np.array([nk.get('scale_reward', 1.), float(nk.get('normalize_obs', False)),
+                                              float(nk.get('normalize_reward', False)),
+                                              nk.get('expected_action_scale', 1.), nk.get('obs_alpha', 0.001),
+                                              nk.get('reward_alpha', 0.001)], np.float64),
+                    name + '_obs_mean': np.asarray(env._obs_mean, np.float64),
+                    name + '_obs_var': np.asarray(env._obs_var, np.float64),
+                    name + '_reward_stats': np.array([env._reward_mean, env._reward_var], np.float64)})
+    np.savez_compressed(os.path.join(OUT, 'normalized_env.npz'), **out)
+
+
 def gen_losses():
     """PPO / VPG / value-function losses and per-parameter gradients from the reference's
     own autograd graph (`_compute_loss_with_adv().backward()`, `compute_loss().backward()`),
@@ -201,6 +254,7 @@ def main():
     os.makedirs(OUT, exist_ok=True)
     gen_gae()
     gen_point_env()
+    gen_normalized_env()
     gen_losses()
     gen_train_once()
     for f in sorted(os.listdir(OUT)):

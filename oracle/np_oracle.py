@@ -231,6 +231,55 @@ def point_step(point, action, goal=(1., 1.), arena_size=5., done_bonus=0., never
     return point, obs, reward, done, succ
 
 
+class NormalizedEnvOracle:
+    """envs/normalized_env.py:8-171 for n independent env copies (each copy owns its running
+    estimates, as every worker's env object does); float64 like the reference's numpy state,
+    float32 for the action arithmetic (float32 action, float32 bounds).
+    Pinned by tests/golden/normalized_env.npz (the reference wrapper around its PointEnv)."""
+
+    def __init__(self, n, obs_dim, act_low, act_high, scale_reward=1., normalize_obs=False,
+                 normalize_reward=False, expected_action_scale=1., obs_alpha=0.001, reward_alpha=0.001):
+        self.lb = np.asarray(act_low, np.float32)
+        self.ub = np.asarray(act_high, np.float32)
+        self.scale_reward, self.normalize_obs, self.normalize_reward = scale_reward, normalize_obs, normalize_reward
+        self.es, self.oa, self.ra = expected_action_scale, obs_alpha, reward_alpha
+        self.obs_mean = np.zeros((n, obs_dim))      # :50-52
+        self.obs_var = np.ones((n, obs_dim))
+        self.reward_mean = np.zeros(n)              # :54-55
+        self.reward_var = np.ones(n)
+        # :91-94, including the reference's `ub != -inf`
+        self.scale_action = bool(np.all(self.lb != -np.inf) and np.all(self.ub != -np.inf))
+
+    def action(self, action):
+        """:91-101: what the wrapped env receives (float32)."""
+        a = np.asarray(action, np.float32)
+        if not self.scale_action:
+            return a
+        es = np.float32(self.es)
+        k = (np.float32(0.5) * (self.ub - self.lb)) / es
+        return np.clip(self.lb + (a + es) * k, self.lb, self.ub).astype(np.float32)
+
+    def obs(self, obs, rows=None):
+        """:117-146 (_update_obs_estimate, _apply_normalize_obs) for the env copies `rows`."""
+        obs = np.asarray(obs)
+        if not self.normalize_obs:
+            return obs
+        r = slice(None) if rows is None else rows
+        o = obs.astype(np.float64)
+        self.obs_mean[r] = (1 - self.oa) * self.obs_mean[r] + self.oa * o
+        self.obs_var[r] = (1 - self.oa) * self.obs_var[r] + self.oa * np.square(o - self.obs_mean[r])
+        return (o - self.obs_mean[r]) / (np.sqrt(self.obs_var[r]) + 1e-8)
+
+    def reward(self, reward):
+        """:124-131, 148-160, then scale_reward (:112)."""
+        rew = np.asarray(reward, np.float64)
+        if self.normalize_reward:
+            self.reward_mean = (1 - self.ra) * self.reward_mean + self.ra * rew
+            self.reward_var = (1 - self.ra) * self.reward_var + self.ra * np.square(rew - self.reward_mean)
+            rew = rew / (np.sqrt(self.reward_var) + 1e-8)
+        return rew * self.scale_reward
+
+
 PENDULUM_PARAMS = dict(max_speed=8., max_torque=2., dt=.05, g=10.0, m=1., l=1.)
 
 
@@ -470,11 +519,12 @@ def env_step_any(env, state, action, kw):
     return s, obs, rew, done, np.zeros(done.shape, bool)
 
 
-def replay_rollout(env, actions, max_episode_length, seed, gid0=0, first_episode=0, env_kw=None):
+def replay_rollout(env, actions, max_episode_length, seed, gid0=0, first_episode=0, env_kw=None, norm=None):
     """Replay recorded actions [T,N,A] through N vectorised envs with the
     bookkeeping of sampler/vec_worker.py:176-204: per-env step counters,
     StepType.get_step_type (_dtypes.py:44-68), last observation kept at the
-    finishing step (Q10), immediate reset of a finished env (:171)."""
+    finishing step (Q10), immediate reset of a finished env (:171).
+    norm: a NormalizedEnvOracle wrapped around every env copy (envs/normalized_env.py)."""
     env_kw = dict(env_kw or {})
     actions = np.asarray(actions, np.float32)
     T, N, A = actions.shape
@@ -482,6 +532,8 @@ def replay_rollout(env, actions, max_episode_length, seed, gid0=0, first_episode
     ep = np.full(N, first_episode, np.int64)
     goal = env_kw.get('goal', (1., 1.))
     state, obs = env_reset_states(env, seed, gid, ep, goal)
+    if norm is not None:
+        obs = norm.obs(obs)
     ep += 1
     O_ = obs.shape[1]
     out = dict(obs=np.zeros((T, N, O_), np.float32), rew=np.zeros((T, N), np.float64),
@@ -490,7 +542,10 @@ def replay_rollout(env, actions, max_episode_length, seed, gid0=0, first_episode
     cnt = np.zeros(N, np.int64)
     for t in range(T):
         out['obs'][t] = obs
-        state, obs, rew, done, succ = env_step_any(env, state, actions[t], env_kw)
+        act_t = actions[t] if norm is None else norm.action(actions[t])
+        state, obs, rew, done, succ = env_step_any(env, state, act_t, env_kw)
+        if norm is not None:
+            obs, rew = norm.obs(obs), norm.reward(rew)
         cnt += 1
         st = np.where(cnt == 1, FIRST, MID)
         st = np.where(done, TERMINAL, st)
@@ -504,6 +559,8 @@ def replay_rollout(env, actions, max_episode_length, seed, gid0=0, first_episode
             out['last_obs'][t][last] = obs[last]
             out['ep_len'][t][last] = cnt[last]
             rs, ro = env_reset_states(env, seed, gid[last], ep[last], goal)
+            if norm is not None:
+                ro = norm.obs(ro, rows=last)
             state = np.array(state)
             obs = np.array(obs)
             state[last] = rs

@@ -53,6 +53,35 @@ def test_point_env_transitions(case):
         assert O.get_step_type(t + 1, int(max_len), bool(done[0])) == d[case + '_step_types'][t]
 
 
+@pytest.mark.parametrize('case', 'abcd')
+def test_normalized_env(case):
+    """oracle NormalizedEnvOracle (+ point_step) vs the reference's normalize(PointEnv) run."""
+    d = load('normalized_env.npz')
+    gx, gy, arena, bonus, never, max_len = d[case + '_env']
+    scale_reward, n_obs, n_rew, es, oa, ra = d[case + '_norm']
+    w = O.NormalizedEnvOracle(1, 3, [-0.1, -0.1], [0.1, 0.1], scale_reward=scale_reward, normalize_obs=bool(n_obs),
+                              normalize_reward=bool(n_rew), expected_action_scale=es, obs_alpha=oa, reward_alpha=ra)
+    acts, obs, first = d[case + '_actions'], d[case + '_obs'], list(d[case + '_first'])
+    k = 0  # row of `obs`: one extra row per reset()
+    cnt = 0
+    for t, a in enumerate(acts):
+        if t in first:
+            point, o0 = O.point_reset(1, (gx, gy))
+            assert np.allclose(w.obs(o0)[0], obs[k], rtol=1e-6, atol=1e-7)
+            k += 1
+            cnt = 0
+        point, o, rew, done, succ = O.point_step(point, w.action(a[None]), goal=(gx, gy), arena_size=arena,
+                                                 done_bonus=bonus, never_done=bool(never))
+        cnt += 1
+        assert np.allclose(w.obs(o)[0], obs[k], rtol=1e-5, atol=1e-6)
+        assert abs(w.reward(rew)[0] - d[case + '_rewards'][t]) <= 1e-5 * max(1, abs(d[case + '_rewards'][t]))
+        assert O.get_step_type(cnt, int(max_len), bool(done[0])) == d[case + '_step_types'][t]
+        k += 1
+    assert np.allclose(w.obs_mean[0], d[case + '_obs_mean'], rtol=1e-5, atol=1e-7)
+    assert np.allclose(w.obs_var[0], d[case + '_obs_var'], rtol=1e-5, atol=1e-7)
+    assert np.allclose([w.reward_mean[0], w.reward_var[0]], d[case + '_reward_stats'], rtol=1e-5, atol=1e-7)
+
+
 @pytest.mark.parametrize('case', ['p64', 'p32', 'c64'])
 def test_losses_gradients_adam(case):
     d = load('losses.npz')
