@@ -227,6 +227,19 @@ def timed(fn, steps, barrier):
     return e0.elapsed_time(e1)
 
 
+def ncu_traffic(kernel, **shape):
+    """dram bytes per launch of `kernel` from the committed `ncu --set full` capture
+    (profiles/r1_ncu_traffic.json) when it was taken on this exact shape, else None."""
+    try:
+        with open(os.path.join(os.path.dirname(os.path.abspath(__file__)), 'profiles', 'r1_ncu_traffic.json')) as fh:
+            rec = json.load(fh)[kernel]
+    except (OSError, KeyError, ValueError):
+        return None
+    if any(rec.get(k) != v for k, v in shape.items()):
+        return None
+    return rec['dram_read_bytes'] + rec['dram_write_bytes']
+
+
 def kernel_rooflines(a, algo, device):
     """Dominant kernel (the fused training loop: every minibatch step of both networks in one
     launch; falls back to the one-minibatch kernel when the loop does not apply) and the GAE
@@ -268,7 +281,10 @@ def kernel_rooflines(a, algo, device):
         steps = a.epochs * -(-B // mb)
         flops = 2 * flops_row * B * a.epochs
         ach = flops / (ms * 1e-3) / 1e12
-        mlp = dict(bound='tensor', achieved=ach, peak=tf, unit='TFLOP/s', frac=ach / tf, traffic=None,
+        mlp = dict(bound='tensor', achieved=ach, peak=tf, unit='TFLOP/s', frac=ach / tf,
+                   traffic=ncu_traffic('train_loop_kernel', rows=B, minibatch=mb, epochs=a.epochs),
+                   traffic_unit='dram bytes per launch (ncu --set full, profiles/r1_ncu_traffic.json); the '
+                                'gathered batch (rows x 40 B per epoch) is L2-resident',
                    kernel='train_loop_kernel<O={},A={}> (tcgen05 kind::tf32, 3xTF32 split: the tensor pipe '
                           'executes 3x the algorithmic FLOPs)'.format(O_, A),
                    us_per_launch=ms * 1e3, minibatch_steps_per_launch=steps, us_per_minibatch_step=ms * 1e3 / steps,
@@ -309,7 +325,9 @@ def kernel_rooflines(a, algo, device):
     torch.cuda.synchronize()
     gms = e0.elapsed_time(e1) / 10
     gbs = 17.0 * T * N / (gms * 1e-3) / 1e9
-    gae = dict(bound='hbm', achieved=gbs, peak=hbm, unit='GB/s', frac=gbs / hbm, traffic=None,
+    gae = dict(bound='hbm', achieved=gbs, peak=hbm, unit='GB/s', frac=gbs / hbm,
+               traffic=ncu_traffic('gae_time_major_kernel', T=T, N=N), algorithmic_bytes=17.0 * T * N,
+               traffic_unit='dram bytes per launch (ncu --set full, profiles/r1_ncu_traffic.json)',
                kernel='gae_time_major_kernel', T=T, N=N, us_per_launch=gms * 1e3,
                footprint_mb=17.0 * T * N / 1e6, peak_kind=kind,
                note='17 algorithmic B per (t,n): r 4 + V 4 + step_type 1 read, A 4 + R 4 written')
