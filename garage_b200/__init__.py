@@ -5,7 +5,9 @@ Everything numerical runs in hand-written sm_100a kernels behind the C ABI of
 `libb2g.so` (include/b2g.h); there is no CPU fallback."""
 from garage_b200._dtypes import DeviceEpisodeBatch, EpisodeBatch, StepType
 from garage_b200._environment import Environment, EnvSpec, EnvStep
+from garage_b200.experiment import wrap_experiment
+from garage_b200.experiment.snapshotter import SnapshotConfig
 from garage_b200.trainer import Trainer
 
 __all__ = ['EpisodeBatch', 'DeviceEpisodeBatch', 'StepType', 'EnvSpec', 'EnvStep', 'Environment',
-           'Trainer']
+           'Trainer', 'wrap_experiment', 'SnapshotConfig']

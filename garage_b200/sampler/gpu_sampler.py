@@ -125,6 +125,13 @@ class GPUSampler(Sampler):
             self._es = ops.EnvState(self._env.env_id, self._n_envs, self._device())
         if self._t_dev is None:
             self._t_dev = torch.zeros(1, dtype=torch.int64, device=self._device())
+        carry = self.__dict__.pop('_carry', None)
+        if carry is not None and carry['env_id'] == self._es.env_id and carry['n'] == self._es.n:
+            # state restored from a snapshot: the random streams continue where they stopped
+            self._t_dev.copy_(carry['t'])
+            self._es.episode.copy_(carry['episode'])
+            if carry['norm_stats'] is not None:
+                self._es.norm_stats = carry['norm_stats'].to(self._device())
 
     def _ensure_buffers(self, rows):
         if self._buf is None or self._buf.T < rows or self._buf.obs.device != self._device():
@@ -243,8 +250,15 @@ class GPUSampler(Sampler):
         self._es = None
         self._buf = None
 
-    def __getstate__(self):  # cloudpickle-able: device buffers are rebuilt lazily
+    def __getstate__(self):
+        """cloudpickle-able: device buffers are rebuilt lazily; what identifies the position in the
+        random streams (Philox step counter, per-env episode counters) and the running estimates
+        of normalize(env) travel as host tensors, so a resumed run continues the same sequence."""
         state = self.__dict__.copy()
+        es = self._es
+        if es is not None and self._t_dev is not None:
+            state['_carry'] = dict(env_id=es.env_id, n=es.n, t=self._t_dev.cpu(), episode=es.episode.cpu(),
+                                   norm_stats=None if es.norm_stats is None else es.norm_stats.cpu())
         state['_es'] = None
         state['_buf'] = None
         state['_t_dev'] = None

@@ -116,6 +116,16 @@ class VPG(RLAlgorithm):
     def discount(self):
         return self._discount
 
+    def __getstate__(self):
+        """Snapshots (trainer.py:263-293) carry parameters, optimiser state and hyper-parameters;
+        the peer-memory communicator and the process group belong to the running job and are
+        re-created on first use after `Trainer.restore`."""
+        state = self.__dict__.copy()
+        state['_comm'] = None
+        state['_pg'] = None
+        state['_dist_B'] = None
+        return state
+
     # ------------------------------------------------------------ distributed --
     def _world(self):
         return _dist.world_size(self._pg)

@@ -6,9 +6,8 @@ accelerated path; a `snapshot_dir` enables a cloudpickle snapshot per epoch
 import os
 import time
 
-import cloudpickle
-
 from garage_b200.experiment import deterministic
+from garage_b200.experiment.snapshotter import Snapshotter, load_snapshot
 from garage_b200.tabular import tabular
 
 
@@ -24,6 +23,10 @@ class TrainArgs:
         self.start_epoch = start_epoch
 
 
+class NotSetupError(Exception):
+    """Reference trainer.py:540."""
+
+
 class Trainer:
     """Sets up and runs the algorithm's epoch loop.
 
@@ -34,6 +37,10 @@ class Trainer:
 
     def __init__(self, snapshot_config=None):
         self._snapshot_config = snapshot_config
+        # reference trainer.py:106-109; no config = no snapshots (the reference always has one)
+        self._snapshotter = None if snapshot_config is None else Snapshotter(
+            snapshot_config.snapshot_dir, snapshot_config.snapshot_mode,
+            snapshot_config.snapshot_gap)
         self._has_setup = False
         self._seed = None
         self._train_args = None
@@ -98,31 +105,29 @@ class Trainer:
         return eps.to_list()
 
     def save(self, epoch):
-        """Reference trainer.py:263-293 (cloudpickle; device buffers are dropped by the
-        classes' __getstate__)."""
-        cfg = self._snapshot_config
-        if cfg is None or getattr(cfg, 'snapshot_mode', 'last') == 'none':
+        """Reference trainer.py:263-293: seed, train_args, stats, env and algo through the
+        Snapshotter (cloudpickle; device buffers are dropped by the classes' __getstate__)."""
+        if not self._has_setup:
+            raise NotSetupError('Use setup() to setup trainer before saving.')
+        if self._snapshotter is None:
             return
         params = dict(seed=self._seed, train_args=self._train_args,
                       stats=dict(total_epoch=self._stats_total_epoch, total_itr=self._stats_total_itr,
-                                 total_env_steps=self._stats_total_env_steps),
+                                 total_env_steps=self._stats_total_env_steps,
+                                 last_episode=self._stats_last_episode),
                       env=self._env, algo=self._algo)
-        os.makedirs(cfg.snapshot_dir, exist_ok=True)
-        mode = getattr(cfg, 'snapshot_mode', 'last')
-        name = 'itr_{}.pkl'.format(epoch) if mode == 'all' else 'params.pkl'
-        with open(os.path.join(cfg.snapshot_dir, name), 'wb') as fh:
-            cloudpickle.dump(params, fh)
+        self._snapshotter.save_itr_params(epoch, params)
 
     def restore(self, from_dir, from_epoch='last'):
-        """Reference trainer.py:295-341."""
-        name = 'params.pkl' if from_epoch == 'last' else 'itr_{}.pkl'.format(from_epoch)
-        with open(os.path.join(from_dir, name), 'rb') as fh:
-            saved = cloudpickle.load(fh)
+        """Reference trainer.py:295-341: load a snapshot, re-seed, set the trainer up with the
+        saved env and algo, continue at the epoch after the saved one.  Returns the TrainArgs."""
+        saved = load_snapshot(from_dir, from_epoch)
         self._seed = saved['seed']
         self._train_args = saved['train_args']
         st = saved['stats']
         self._stats_total_epoch, self._stats_total_itr = st['total_epoch'], st['total_itr']
         self._stats_total_env_steps = st['total_env_steps']
+        self._stats_last_episode = st.get('last_episode')
         if self._seed is not None:
             deterministic.set_seed(self._seed)
         self.setup(env=saved['env'], algo=saved['algo'])
@@ -134,12 +139,13 @@ class Trainer:
         tabular.record('Time', time.time() - self._start_time)
         tabular.record('EpochTime', time.time() - self._itr_start_time)
         self.log.append(tabular.as_dict)
+        tabular.dump()
 
     def train(self, n_epochs, batch_size=None, plot=False, store_episodes=False,
               pause_for_plot=False):
         """Reference trainer.py:361-405."""
         if not self._has_setup:
-            raise Exception('Use setup() to setup trainer before training.')
+            raise NotSetupError('Use setup() to setup trainer before training.')
         if plot:
             raise NotImplementedError('plotting is unavailable on this box (no graphics stack)')
         self._train_args = TrainArgs(n_epochs=n_epochs, batch_size=batch_size, plot=plot,
@@ -162,7 +168,7 @@ class Trainer:
             self._itr_start_time = time.time()
             tabular.clear()
             yield epoch
-            self._stats_last_episode = self.step_episode if self.step_episode is not None else None
+            self._stats_last_episode = self.step_episode if self._train_args.store_episodes else None  # trainer.py:443-446
             self._stats_total_epoch = epoch
             self._stats_total_itr = self.step_itr
             self.save(epoch)
@@ -172,7 +178,7 @@ class Trainer:
     def resume(self, n_epochs=None, batch_size=None):
         """Reference trainer.py:457-500."""
         if self._train_args is None:
-            raise Exception('You must restore a checkpoint before resume.')
+            raise NotSetupError('You must restore a checkpoint before resume.')
         self._train_args.n_epochs = n_epochs or self._train_args.n_epochs
         self._train_args.batch_size = batch_size or self._train_args.batch_size
         average_return = self._algo.train(self)
