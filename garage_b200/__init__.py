@@ -8,6 +8,9 @@ from garage_b200._environment import Environment, EnvSpec, EnvStep
 from garage_b200.experiment import wrap_experiment
 from garage_b200.experiment.snapshotter import SnapshotConfig
 from garage_b200.trainer import Trainer
+from garage_b200._functions import (log_multitask_performance, log_performance,
+                                    obtain_evaluation_episodes)
 
 __all__ = ['EpisodeBatch', 'DeviceEpisodeBatch', 'StepType', 'EnvSpec', 'EnvStep', 'Environment',
-           'Trainer', 'wrap_experiment', 'SnapshotConfig']
+           'Trainer', 'wrap_experiment', 'SnapshotConfig',
+           'log_performance', 'log_multitask_performance', 'obtain_evaluation_episodes']

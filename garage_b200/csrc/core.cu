@@ -191,3 +191,139 @@ extern "C" int b2g_permutation(uint64_t seed, const unsigned long long* counter_
     B2G_CHECK_LAUNCH();
     return B2G_OK;
 }
+
+// ---------------------------------------------------------- episode stats --
+// log_performance (_functions.py:233-275) over an episode-major packed batch: per episode
+// the undiscounted return sum_t r_t, the discounted return sum_t gamma^t r_t (what
+// discount_cumsum(rewards, gamma)[0] is, np/_functions.py:111-128, float64 like the reference's
+// rewards), whether any of its steps is TERMINAL and whether any step reports success.
+// One warp per episode.  Lane l owns steps l, l+32, ...: a reverse Horner pass in gamma^32 gives
+// sum_k r[l+32k] gamma^(32k); the lanes are then combined as sum_l gamma^l (.) by an xor
+// butterfly, so the order of additions depends on the episode length only (deterministic).
+// fixed_len > 0: episode e spans [e*fixed_len, (e+1)*fixed_len); else offsets[e], lengths[e].
+template <typename R>
+__global__ void __launch_bounds__(256)
+episode_stats_kernel(const R* __restrict__ rew, const uint8_t* __restrict__ step_type,
+                     const uint8_t* __restrict__ success, const int64_t* __restrict__ lengths,
+                     const int64_t* __restrict__ offsets, int64_t fixed_len, double gamma,
+                     int64_t n_eps, double* __restrict__ per_ep) {
+    const int lane = threadIdx.x & 31;
+    const int64_t e = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    if (e >= n_eps) return;
+    const int64_t len = fixed_len > 0 ? fixed_len : lengths[e];
+    const int64_t off = fixed_len > 0 ? e * fixed_len : offsets[e];
+    double g32 = gamma;
+#pragma unroll
+    for (int i = 0; i < 5; ++i) g32 *= g32;
+    double und = 0.0, disc = 0.0;
+    int succ = 0, term = 0;
+    if (lane < len) {
+        const int64_t k_last = (len - 1 - lane) / 32;
+        for (int64_t k = k_last; k >= 0; --k) {
+            const int64_t t = off + lane + 32 * k;
+            const double r = (double)rew[t];
+            und += r;
+            disc = fma(disc, g32, r);
+            if (success) succ |= success[t] != 0;
+            if (step_type) term |= step_type[t] == ST_TERMINAL;  // any(step_type == TERMINAL), :254-256
+        }
+    }
+    double gl = 1.0;  // gamma^lane by repeated squaring over the bits of lane
+    {
+        double b = gamma;
+        for (int m = lane; m; m >>= 1) {
+            if (m & 1) gl *= b;
+            b *= b;
+        }
+    }
+    disc *= gl;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        und += __shfl_xor_sync(0xffffffffu, und, o);
+        disc += __shfl_xor_sync(0xffffffffu, disc, o);
+        succ |= __shfl_xor_sync(0xffffffffu, succ, o);
+        term |= __shfl_xor_sync(0xffffffffu, term, o);
+    }
+    if (lane == 0) {
+        per_ep[e] = und;
+        per_ep[n_eps + e] = disc;
+        per_ep[2 * n_eps + e] = term ? 1.0 : 0.0;
+        per_ep[3 * n_eps + e] = succ ? 1.0 : 0.0;
+    }
+}
+
+// out7 = [mean disc, mean und, population std und (np.std), max und, min und, termination rate,
+// success rate (NaN without a success field)]: one block, fixed strides and tree => deterministic.
+__global__ void __launch_bounds__(1024)
+episode_summary_kernel(const double* __restrict__ per_ep, int64_t n_eps, int has_success,
+                       double* __restrict__ out7) {
+    __shared__ double sh[32];
+    __shared__ double bcast;
+    const int tid = threadIdx.x;
+    double s_und = 0, s_disc = 0, s_term = 0, s_succ = 0, mx = -INFINITY, mn = INFINITY;
+    for (int64_t e = tid; e < n_eps; e += blockDim.x) {
+        const double u = per_ep[e];
+        s_und += u;
+        s_disc += per_ep[n_eps + e];
+        s_term += per_ep[2 * n_eps + e];
+        s_succ += per_ep[3 * n_eps + e];
+        mx = fmax(mx, u);
+        mn = fmin(mn, u);
+    }
+    const double n = (double)n_eps;
+    s_und = block_reduce_sum(s_und, sh);
+    if (tid == 0) bcast = s_und / n;
+    __syncthreads();
+    const double mean = bcast;
+    double ss = 0;
+    for (int64_t e = tid; e < n_eps; e += blockDim.x) {
+        const double d = per_ep[e] - mean;
+        ss += d * d;
+    }
+    ss = block_reduce_sum(ss, sh);
+    s_disc = block_reduce_sum(s_disc, sh);
+    s_term = block_reduce_sum(s_term, sh);
+    s_succ = block_reduce_sum(s_succ, sh);
+    // max / min: order-independent, reuse the sum tree's staging with fmax/fmin
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        mx = fmax(mx, __shfl_down_sync(0xffffffffu, mx, o));
+        mn = fmin(mn, __shfl_down_sync(0xffffffffu, mn, o));
+    }
+    __shared__ double shx[32], shn[32];
+    if ((tid & 31) == 0) { shx[tid >> 5] = mx; shn[tid >> 5] = mn; }
+    __syncthreads();
+    if (tid == 0) {
+        for (int w = 1; w < (int)(blockDim.x >> 5); ++w) { mx = fmax(mx, shx[w]); mn = fmin(mn, shn[w]); }
+        out7[0] = s_disc / n;
+        out7[1] = mean;
+        out7[2] = sqrt(ss / n);
+        out7[3] = mx;
+        out7[4] = mn;
+        out7[5] = s_term / n;
+        out7[6] = has_success ? s_succ / n : nan("");
+    }
+}
+
+extern "C" int b2g_episode_stats(const void* rewards, int rewards_f64, const uint8_t* step_type,
+                                 const uint8_t* success, const int64_t* lengths, const int64_t* offsets,
+                                 int64_t fixed_len, double discount, int64_t n_eps, double* per_episode4,
+                                 double* out7, void* stream) {
+    B2G_CHECK_ARG(n_eps > 0, "n_eps must be positive");
+    B2G_CHECK_ARG(rewards && per_episode4, "NULL pointer");
+    B2G_CHECK_ARG(fixed_len > 0 || (lengths && offsets), "ragged episodes need lengths and offsets");
+    cudaStream_t s = (cudaStream_t)stream;
+    const unsigned blocks = (unsigned)((n_eps * 32 + 255) / 256);
+    if (rewards_f64)
+        episode_stats_kernel<double><<<blocks, 256, 0, s>>>((const double*)rewards, step_type, success, lengths,
+                                                            offsets, fixed_len, discount, n_eps, per_episode4);
+    else
+        episode_stats_kernel<float><<<blocks, 256, 0, s>>>((const float*)rewards, step_type, success, lengths,
+                                                           offsets, fixed_len, discount, n_eps, per_episode4);
+    B2G_CHECK_LAUNCH();
+    if (out7) {
+        episode_summary_kernel<<<1, 1024, 0, s>>>(per_episode4, n_eps, success != nullptr, out7);
+        B2G_CHECK_LAUNCH();
+    }
+    return B2G_OK;
+}

@@ -102,6 +102,38 @@ def moments(x, out=None):
     return out
 
 
+def episode_stats(rewards, discount, step_types=None, success=None, lengths=None, fixed_len=None, out=None):
+    """b2g_episode_stats over a packed episode-major batch.  Returns (per_episode [4, n_eps] f64:
+    undiscounted return, discounted return, terminated, success; summary [7] f64)."""
+    if rewards.dtype not in (torch.float32, torch.float64):
+        raise TypeError('rewards must be float32 or float64')
+    _chk(rewards, rewards.dtype, 'rewards')
+    _chk(step_types, torch.uint8, 'step_types')
+    _chk(success, torch.uint8, 'success')
+    _chk(lengths, torch.int64, 'lengths')
+    B = rewards.numel()
+    if fixed_len:
+        if B % int(fixed_len):
+            raise ValueError('fixed_len does not divide the batch')
+        n_eps, offsets = B // int(fixed_len), None
+    else:
+        if lengths is None:
+            raise ValueError('need lengths or fixed_len')
+        n_eps = lengths.numel()
+        offsets = torch.cumsum(lengths, 0) - lengths
+    if n_eps == 0:
+        raise ValueError('no episodes')
+    per = torch.empty(4, n_eps, dtype=torch.float64, device=rewards.device)
+    if out is None:
+        out = torch.empty(7, dtype=torch.float64, device=rewards.device)
+    _chk(out, torch.float64, 'out')
+    with torch.cuda.device(rewards.device):
+        call('b2g_episode_stats', ptr(rewards), int(rewards.dtype == torch.float64), ptr(step_types),
+             ptr(success), ptr(lengths), ptr(offsets), int(fixed_len or 0), float(discount), int(n_eps),
+             ptr(per), ptr(out), _stream(rewards))
+    return per, out
+
+
 def normalize_adv(x, stats, center_adv=True, positive_adv=False, out=None):
     _chk(x, torch.float32, 'x')
     _chk(stats, torch.float64, 'stats')

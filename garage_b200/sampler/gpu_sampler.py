@@ -21,7 +21,7 @@ import torch
 
 from garage_b200 import ops
 from garage_b200._dtypes import DeviceEpisodeBatch
-from garage_b200.experiment import deterministic
+from garage_b200.experiment import deterministic as _seeding
 
 
 class _LazyLogStd:
@@ -66,13 +66,16 @@ class GPUSampler(Sampler):
         max_episode_length (int): required, like the reference (local_sampler.py:63-65).
         n_envs (int): environment copies on this rank.
         seed (int): Philox key (defaults to `deterministic.get_seed()` or 0).
+        deterministic (bool): act with the mean of the action distribution (evaluation rollouts,
+            np/_functions.py rollout(deterministic=True)); log-probs of such a batch are undefined.
         env_id_offset (int): global id of this rank's first env (rank * n_envs), so
             results do not depend on how envs are sharded over GPUs.
     """
 
     def __init__(self, agents, envs, *, worker_factory=None, max_episode_length=None,
                  is_tf_worker=False, seed=None, n_workers=None, worker_class=VecWorker,
-                 worker_args=None, n_envs=None, env_id_offset=0, keep_agent_infos=True):
+                 worker_args=None, n_envs=None, env_id_offset=0, keep_agent_infos=True,
+                 deterministic=False):
         if worker_factory is None and max_episode_length is None:
             raise TypeError('Must construct a sampler from WorkerFactory or parameters (at least '
                             'max_episode_length)')
@@ -91,10 +94,11 @@ class GPUSampler(Sampler):
         self._max_episode_length = max_episode_length
         self._n_envs = int(n_envs)
         if seed is None:
-            seed = deterministic.get_seed()
+            seed = _seeding.get_seed()
         self._seed = 0 if seed is None else int(seed)
         self._env_id_offset = int(env_id_offset)
         self._keep_agent_infos = keep_agent_infos
+        self._deterministic = bool(deterministic)
         self._t_dev = None  # device-side global step counter (Philox counter word)
         self._es = None
         self._buf = None
@@ -119,6 +123,10 @@ class GPUSampler(Sampler):
         if m is None or (isinstance(m, float) and math.isinf(m)):
             return 0
         return int(m)
+
+    def _max_log_std(self):
+        # b2g_rollout: max_log_std = -inf clamps the std to exactly 0, i.e. action = mean
+        return -math.inf if self._deterministic else self._policy._module.max_log_std
 
     def _ensure_state(self):
         if self._es is None or self._es.env_id != self._env.env_id:
@@ -184,7 +192,7 @@ class GPUSampler(Sampler):
         done_rows = 0
         while True:
             ops.rollout(self._es, prm, L, pol.flat, pol.mlp_shape.H, pol._module.min_log_std,
-                        pol._module.max_log_std, self._seed, self._env_id_offset, 0,
+                        self._max_log_std(), self._seed, self._env_id_offset, 0,
                         self._buf, done_rows, rows - done_rows, t_counter_dev=self._t_dev, norm=norm)
             ops.counter_add(self._t_dev, rows - done_rows)
             done_rows = rows
@@ -241,9 +249,62 @@ class GPUSampler(Sampler):
             lengths_host=np.full(n_eps, self._max_len(), dtype=np.int64) if static else None)
 
     def obtain_exact_episodes(self, n_eps_per_worker, agent_update, env_update=None):
-        """`n_eps_per_worker` whole episodes from EVERY env copy, env-major order
-        (reference local_sampler.py:168-200 with one env per worker)."""
-        raise NotImplementedError('obtain_exact_episodes is not on the PPO/VPG path; use obtain_samples')
+        """Exactly `n_eps_per_worker` whole episodes from EVERY env copy, env-major order (reference
+        local_sampler.py:168-200 with one env per worker): every env runs from `reset()` for
+        n_eps_per_worker * max_episode_length steps, all episodes completed by then are packed and
+        the first n_eps_per_worker of each env are kept."""
+        k = int(n_eps_per_worker)
+        if k <= 0:
+            raise ValueError('n_eps_per_worker must be positive')
+        self._update(agent_update, env_update)
+        env, N, L = self._env, self._n_envs, self._max_len()
+        if L == 0:
+            raise ValueError('obtain_exact_episodes needs a finite max_episode_length')
+        self._ensure_state()
+        prm, pol = env.params_array(), self._policy
+        norm = env.norm_config() if hasattr(env, 'norm_config') else None
+        ops.env_reset(self._es, prm, self._seed, self._env_id_offset, norm=norm)
+        rows = k * L
+        self._ensure_buffers(rows)
+        ops.rollout(self._es, prm, L, pol.flat, pol.mlp_shape.H, pol._module.min_log_std,
+                    self._max_log_std(), self._seed, self._env_id_offset, 0, self._buf, 0, rows,
+                    t_counter_dev=self._t_dev, norm=norm)
+        ops.counter_add(self._t_dev, rows)
+        ws, (t_star, n_eps, n_steps, _) = self._plan(rows, N * rows + 1, sync=True)
+        full = self._pack(ws, rows, t_star, n_eps, n_steps, static=False)
+        batch = self._select_first(full, k)
+        self.total_env_steps += batch.n_steps
+        return batch
+
+    def _select_first(self, full, k):
+        """The first k episodes of every env out of a packed batch, reordered env-major.
+        Index arithmetic on the device (not on the training path: evaluation batches)."""
+        d, N = full.dev, self._n_envs
+        n_all = full.n_episodes
+        ep_env = d.ep_env.to(torch.int64)
+        # episodes are in completion order, so a stable sort by env keeps each env's own order
+        order = torch.sort(ep_env, stable=True).indices
+        first_of_env = torch.searchsorted(ep_env[order], torch.arange(N, device=ep_env.device))
+        rank = torch.arange(n_all, device=ep_env.device) - first_of_env[ep_env[order]]
+        keep = order[rank < k]  # env-major, completion order inside an env
+        if keep.numel() != N * k:
+            raise RuntimeError('an env completed fewer than {} episodes'.format(k))
+        off_all = torch.cumsum(d.lengths, 0) - d.lengths
+        lengths = d.lengths[keep]
+        new_off = torch.cumsum(lengths, 0) - lengths
+        n_steps = int(lengths.sum().item())
+        ep_of_row = torch.repeat_interleave(torch.arange(keep.numel(), device=keep.device), lengths,
+                                            output_size=n_steps)
+        rows = off_all[keep][ep_of_row] + (torch.arange(n_steps, device=keep.device) - new_off[ep_of_row])
+        dev = DeviceEpisodeBatch._Dev()
+        for name in ('observations', 'actions', 'rewards', 'logp', 'step_types', 'mean', 'success'):
+            t = getattr(d, name)
+            setattr(dev, name, None if t is None else t[rows].contiguous())
+        dev.last_observations, dev.lengths = d.last_observations[keep].contiguous(), lengths
+        dev.ep_env, dev.ep_end = d.ep_env[keep], d.ep_end[keep]
+        return DeviceEpisodeBatch(
+            env_spec=full.env_spec, dev=dev, n_eps=keep.numel(), n_steps=n_steps, log_std=full._log_std,
+            episode_info_consts=full._episode_info_consts, env_info_consts=full._env_info_consts)
 
     def shutdown_worker(self):
         """Nothing to shut down: there are no worker processes."""

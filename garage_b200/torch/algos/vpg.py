@@ -405,32 +405,13 @@ class VPG(RLAlgorithm):
         self._run_minibatches(self._vf_optimizer, self._value_function, f, policy=False)
 
     def _performance(self, f, out):
-        """log_performance (_functions.py:233-275) as device reductions: out[0:6] =
-        [mean discounted return, mean/std/max/min undiscounted return, termination rate],
-        out[6] = success rate (nan when the env reports no 'success')."""
-        n_eps = f.n_eps
-        if f.fixed_len:
-            und = f.rew.view(n_eps, f.fixed_len).sum(1, dtype=torch.float64)
-            first = torch.arange(0, f.B, f.fixed_len, device=f.rew.device)
-        else:
-            und = torch.segment_reduce(f.rew.to(torch.float64), 'sum', lengths=f.lengths)
-            first = torch.cumsum(f.lengths, 0) - f.lengths
-        last = (first + (f.fixed_len if f.fixed_len else f.lengths)) - 1
-        out[0] = f.ret[first].to(torch.float64).mean()
-        out[1] = und.mean()
-        out[2] = und.std(unbiased=False)
-        out[3] = und.max()
-        out[4] = und.min()
-        out[5] = (f.step_types[last] == int(StepType.TERMINAL)).to(torch.float64).mean()
-        if f.success is not None:
-            if f.fixed_len:
-                s = f.success.view(n_eps, f.fixed_len).max(1).values
-            else:
-                s = torch.segment_reduce(f.success.to(torch.float32), 'max', lengths=f.lengths)
-            out[6] = s.to(torch.float64).mean()
-        else:
-            out[6:7].fill_(float('nan'))
-        return und
+        """log_performance (_functions.py:233-275) on the device (b2g_episode_stats): out[0:7] =
+        [mean discounted return, mean/std/max/min undiscounted return, termination rate,
+        success rate (nan when the env reports no 'success')].  Returns the undiscounted returns."""
+        per, _ = ops.episode_stats(f.rew, self._discount, step_types=f.step_types, success=f.success,
+                                   lengths=None if f.fixed_len else f.lengths, fixed_len=f.fixed_len,
+                                   out=out[0:7])
+        return per[0]
 
     def _enqueue_iteration(self, eps):
         """Everything of `_train_once` that runs on the device, without any host

@@ -96,6 +96,21 @@ int b2g_moments(const float* x, int64_t n, double* out3, void* ws, void* stream)
 int b2g_normalize_adv(const float* x, const double* stats3, int center_adv,
                       int positive_adv, float* y, int64_t n, void* stream);
 
+/* b2g_episode_stats: log_performance (_functions.py:233-275) over an episode-major packed
+ * batch.  rewards[B] float32 (rewards_f64 = 0) or float64 (1, the reference's dtype);
+ * step_type[B] StepType codes (may be NULL: termination column = 0); success[B] u8 or NULL.
+ * Episode e spans [e*fixed_len, (e+1)*fixed_len) when fixed_len > 0, else
+ * [offsets[e], offsets[e] + lengths[e]).  per_episode4 = double[4][n_eps]: undiscounted return
+ * (_functions.py:260), discounted return sum_t discount^t r_t (== discount_cumsum(r)[0],
+ * _functions.py:251, float64 accumulation), any step TERMINAL (0/1, :254-256), any success
+ * (0/1, :257-258).  out7 (may be NULL) = the values log_performance records: mean discounted
+ * return, mean / population std / max / min undiscounted return, termination rate, success
+ * rate (NaN when success is NULL). */
+int b2g_episode_stats(const void* rewards, int rewards_f64, const uint8_t* step_type,
+                      const uint8_t* success, const int64_t* lengths, const int64_t* offsets,
+                      int64_t fixed_len, double discount, int64_t n_eps, double* per_episode4,
+                      double* out7, void* stream);
+
 /* ------------------------------------------------------------------ envs --
  * GPU-resident batched environments.  env_id selects the dynamics; `params`
  * is a HOST array of B2G_ENV_NPARAMS doubles:
