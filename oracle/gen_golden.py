@@ -247,6 +247,64 @@ def gen_train_once():
     np.savez_compressed(os.path.join(OUT, 'train_once.npz'), **out)
 
 
+def gen_gridworld():
+    """GridWorldEnv + ScriptedPolicy through the reference's own VecWorker / LocalSampler
+    (the setting of tests/garage/sampler/test_vec_worker.py): integer observations, actions,
+    step types and lengths for the bit-exact GPU parity test.  One case per built-in map; the
+    4x4 cases use the action table of the reference test, the chain walks left to the goal, the
+    others use seeded random tables."""
+    from garage.envs import GridWorldEnv
+    from garage.envs.grid_world_env import MAPS
+    from garage.np.policies import ScriptedPolicy
+    from garage.sampler import LocalSampler, VecWorker, WorkerFactory
+    out = {}
+    rng = np.random.RandomState(7)
+    ref_table = [2, 2, 1, 0, 3, 1, 1, 1, 2, 2, 1, 1, 1, 2, 2, 1]  # test_vec_worker.py:22-31
+    cases = [('4x4', ref_table, 16, 3), ('4x4', ref_table, 4, 3), ('8x8', None, 25, 4),
+             ('chain', [0] * 29, 40, 2), ('4x4_safe', None, 9, 5), ('8x8', None, 200, 2)]
+    for k, (desc, table, max_len, n_envs) in enumerate(cases):
+        n_cells = sum(len(r) for r in MAPS[desc])
+        if table is None:
+            # random tables mostly wander until the time limit: for the odd cases draw (at most 500
+            # times) until the walk from the start ends in a hole or at the goal
+            for _ in range(500):
+                table = [int(v) for v in rng.randint(0, 4, size=n_cells)]
+                probe = GridWorldEnv(desc=desc, max_episode_length=max_len)
+                obs, _ = probe.reset()
+                for _ in range(max_len):
+                    es = probe.step(table[obs])
+                    obs = es.observation
+                    if es.last:
+                        break
+                if k % 2 == 0 or es.terminal:
+                    break
+        env = GridWorldEnv(desc=desc, max_episode_length=max_len)
+        policy = ScriptedPolicy(scripted_actions=table)
+        wf = WorkerFactory(max_episode_length=max_len, n_workers=1, worker_class=VecWorker,
+                           worker_args=dict(n_envs=n_envs))
+        sampler = LocalSampler.from_worker_factory(wf, policy, env)
+        num_samples = 6 * max_len * n_envs // 2 + 1
+        eps = sampler.obtain_samples(0, num_samples, None)
+        pre = 'c{}_'.format(k)
+        out[pre + 'desc'] = np.array(desc)
+        out[pre + 'cells'] = np.array([list(r) for r in MAPS[desc]])
+        out[pre + 'table'] = np.asarray(table, dtype=np.int32)
+        out[pre + 'max_len'] = np.int64(max_len)
+        out[pre + 'n_envs'] = np.int64(n_envs)
+        out[pre + 'num_samples'] = np.int64(num_samples)
+        out[pre + 'observations'] = np.asarray(eps.observations).astype(np.int64).reshape(-1)
+        out[pre + 'last_observations'] = np.asarray(eps.last_observations).astype(np.int64).reshape(-1)
+        out[pre + 'actions'] = np.asarray(eps.actions).astype(np.int64).reshape(-1)
+        out[pre + 'rewards'] = np.asarray(eps.rewards, dtype=np.float64)
+        out[pre + 'step_types'] = np.asarray([int(s) for s in eps.step_types], dtype=np.uint8)
+        out[pre + 'lengths'] = np.asarray(eps.lengths, dtype=np.int64)
+        print('gridworld case', k, desc, 'episodes', len(eps.lengths), 'steps', int(eps.lengths.sum()),
+              'obs shape', np.asarray(eps.observations).shape, np.asarray(eps.observations).dtype,
+              'returns', float(eps.rewards.sum()))
+    out['n_cases'] = np.int64(len(cases))
+    np.savez_compressed(os.path.join(OUT, 'gridworld.npz'), **out)
+
+
 def main():
     from oracle import ref_shims
     if not ref_shims.install():
@@ -257,6 +315,7 @@ def main():
     gen_normalized_env()
     gen_losses()
     gen_train_once()
+    gen_gridworld()
     for f in sorted(os.listdir(OUT)):
         print(f, os.path.getsize(os.path.join(OUT, f)))
 

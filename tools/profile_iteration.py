@@ -15,7 +15,7 @@ def main():
     ap.add_argument('--iters', type=int, default=2)
     ap.add_argument('--epochs', type=int, default=10)
     ap.add_argument('--n-envs', type=int, default=4096)
-    ap.add_argument('--minibatch', type=int, default=32768)
+    ap.add_argument('--minibatch', type=int, default=37888)
     p = ap.parse_args()
     a = argparse.Namespace(n_envs=p.n_envs, horizon=200, hidden=64, epochs=p.epochs, minibatch=p.minibatch)
     algo, policy, vf, sampler = bench.build_algo(a, 0, 1, torch.device('cuda:0'))

@@ -14,7 +14,7 @@ from garage_b200 import ops  # noqa: E402
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument('--rows', type=int, default=819200)
-    ap.add_argument('--mb', type=int, default=32768)
+    ap.add_argument('--mb', type=int, default=37888)
     ap.add_argument('--epochs', type=int, default=2)
     ap.add_argument('--timing', action='store_true')
     ap.add_argument('--single', action='store_true', help='policy network only')
