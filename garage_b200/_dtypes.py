@@ -317,17 +317,23 @@ class DeviceEpisodeBatch(EpisodeBatch):
     def lengths(self):
         return self._get('lengths', lambda: self._host('lengths'))
 
+    def _host_field(self, name):
+        """Discrete spaces (GridWorld): the device holds int32 [n, 1]; the reference's batches hold
+        int64 (n,) (vec_worker.py:206-219 over python ints)."""
+        arr = self._host(name)
+        return arr.reshape(-1).astype(np.int64) if arr.dtype == np.int32 else arr
+
     @property
     def observations(self):
-        return self._get('observations', lambda: self._host('observations'))
+        return self._get('observations', lambda: self._host_field('observations'))
 
     @property
     def last_observations(self):
-        return self._get('last_observations', lambda: self._host('last_observations'))
+        return self._get('last_observations', lambda: self._host_field('last_observations'))
 
     @property
     def actions(self):
-        return self._get('actions', lambda: self._host('actions'))
+        return self._get('actions', lambda: self._host_field('actions'))
 
     @property
     def rewards(self):
@@ -341,6 +347,8 @@ class DeviceEpisodeBatch(EpisodeBatch):
     @property
     def agent_infos(self):
         def make():
+            if self.dev.mean is None:  # scripted / agent-info-free rollouts
+                return {}
             mean = self._host('mean')
             return dict(mean=mean, log_std=np.full_like(mean, np.float32(self.log_std)))
         return self._get('agent_infos', make)

@@ -56,6 +56,8 @@ SIGNATURES = {
     'b2g_discount_cumsum_f64': (c_int, [P, c_double, P, c_int64, c_int, P]),
     'b2g_moments_ws_bytes': (c_int64, []),
     'b2g_moments': (c_int, [P, c_int64, P, P, P]),
+    'b2g_gridworld_step': (c_int, [P, c_int, c_int, c_int, P, P, P, P, P, P, P, c_int64, P]),
+    'b2g_gridworld_rollout': (c_int, [P, c_int, c_int, c_int, c_int, P, P, P, c_int, c_int64, P, P, P, P, P, P, P]),
     'b2g_episode_stats': (c_int, [P, c_int, P, P, P, P, c_int64, c_double, c_int64, P, P, P]),
     'b2g_normalize_adv': (c_int, [P, P, c_int, c_int, P, c_int64, P]),
     'b2g_permutation': (c_int, [c_uint64, P, c_uint64, c_int64, P, P]),

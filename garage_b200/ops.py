@@ -557,3 +557,64 @@ def permutation(n, seed, counter=0, counter_dev=None, out=None, device=None):
         call('b2g_permutation', int(seed) & (2**64 - 1), ptr(counter_dev), int(counter), int(n),
              ptr(out), _stream(out))
     return out
+
+
+# ------------------------------------------------------------- GridWorld --
+class GridState:
+    """Device state of N GridWorld env copies: cells u8 [n_row*n_col], state / step_cnt int32 [N]."""
+
+    def __init__(self, cells, n_row, n_col, start_state, n, device):
+        self.n_row, self.n_col, self.start, self.n, self.device = int(n_row), int(n_col), int(start_state), int(n), device
+        self.cells = torch.as_tensor(cells, dtype=torch.uint8).reshape(-1).to(device)
+        self.state = torch.full((n, ), self.start, dtype=torch.int32, device=device)
+        self.step_cnt = torch.full((n, ), -1, dtype=torch.int32, device=device)
+
+    def reset(self):
+        self.state.fill_(self.start)
+        self.step_cnt.zero_()
+
+
+class GridBuffers:
+    """Time-major [T, N] rollout buffers of b2g_gridworld_rollout."""
+
+    def __init__(self, T, n, device):
+        self.T = int(T)
+        i32 = dict(dtype=torch.int32, device=device)
+        self.obs = torch.empty(T, n, 1, **i32)
+        self.act = torch.empty(T, n, 1, **i32)
+        self.rew = torch.empty(T, n, dtype=torch.float32, device=device)
+        self.step_type = torch.empty(T, n, dtype=torch.uint8, device=device)
+        self.last_obs = torch.zeros(T, n, 1, **i32)
+        self.ep_len = torch.zeros(T, n, **i32)
+
+
+def gridworld_step(gs, max_episode_length, actions):
+    """Environment.step for all envs; returns (obs int32 [N], reward f32 [N], step_type u8 [N])."""
+    _chk(actions, torch.int32, 'actions')
+    if actions.shape != (gs.n, ):
+        raise ValueError('actions must be int32 [{}]'.format(gs.n))
+    obs = torch.empty(gs.n, dtype=torch.int32, device=gs.device)
+    rew = torch.empty(gs.n, dtype=torch.float32, device=gs.device)
+    st = torch.empty(gs.n, dtype=torch.uint8, device=gs.device)
+    err = torch.zeros(1, dtype=torch.int32, device=gs.device)
+    with torch.cuda.device(gs.device):
+        call('b2g_gridworld_step', ptr(gs.cells), gs.n_row, gs.n_col, int(max_episode_length or 0), ptr(gs.state),
+             ptr(gs.step_cnt), ptr(actions), ptr(obs), ptr(rew), ptr(st), ptr(err), gs.n, _stream(actions))
+    bad = int(err.item())
+    if bad:
+        raise RuntimeError('reset() must be called before step()! (env {}, or an action outside 0..3)'.format(bad - 1))
+    return obs, rew, st
+
+
+def gridworld_rollout(gs, max_episode_length, table, buf, t0, n_steps):
+    """b2g_gridworld_rollout into rows t0..t0+n_steps of `buf`."""
+    _chk(table, torch.int32, 'table')
+    if table.numel() != gs.cells.numel():
+        raise ValueError('scripted_actions needs one action per grid cell')
+    if t0 + n_steps > buf.T:
+        raise ValueError('rollout rows exceed the buffer')
+    with torch.cuda.device(gs.device):
+        call('b2g_gridworld_rollout', ptr(gs.cells), gs.n_row, gs.n_col, gs.start, int(max_episode_length or 0),
+             ptr(table), ptr(gs.state), ptr(gs.step_cnt), int(n_steps), gs.n, ptr(buf.obs[t0:]), ptr(buf.act[t0:]),
+             ptr(buf.rew[t0:]), ptr(buf.step_type[t0:]), ptr(buf.last_obs[t0:]), ptr(buf.ep_len[t0:]),
+             _stream(table))

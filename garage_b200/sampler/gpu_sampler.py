@@ -101,6 +101,7 @@ class GPUSampler(Sampler):
         self._deterministic = bool(deterministic)
         self._t_dev = None  # device-side global step counter (Philox counter word)
         self._es = None
+        self._gs = None  # GridWorld device state (GridWorldEnv + ScriptedPolicy path)
         self._buf = None
         self.total_env_steps = 0
 
@@ -116,7 +117,9 @@ class GPUSampler(Sampler):
         return self._n_envs
 
     def _device(self):
-        return self._policy.flat.device
+        if hasattr(self._policy, 'flat'):
+            return self._policy.flat.device
+        return torch.device('cuda', torch.cuda.current_device())
 
     def _max_len(self):
         m = self._max_episode_length
@@ -167,6 +170,8 @@ class GPUSampler(Sampler):
     def obtain_samples(self, itr, num_samples, agent_update, env_update=None):
         """Collect at least `num_samples` transitions (reference
         local_sampler.py:134-166).  Returns a DeviceEpisodeBatch."""
+        if getattr(self._env if env_update is None else env_update, 'env_id', None) == 'gridworld':
+            return self._obtain_gridworld(num_samples, agent_update, env_update)
         self._update(agent_update, env_update)
         env, N = self._env, self._n_envs
         L = self._max_len()
@@ -248,6 +253,59 @@ class GPUSampler(Sampler):
             episode_info_consts=env.episode_info(), env_info_consts=env.env_info_consts(),
             lengths_host=np.full(n_eps, self._max_len(), dtype=np.int64) if static else None)
 
+    def _obtain_gridworld(self, num_samples, agent_update, env_update):
+        """GridWorldEnv + ScriptedPolicy: the VecWorker loop as one integer kernel
+        (b2g_gridworld_rollout), packed by the same pack kernels as every other batch."""
+        if env_update is not None:
+            self._env, self._gs = env_update, None
+        if agent_update is not None and hasattr(agent_update, 'action_table'):
+            self._policy = agent_update
+        env, pol, N = self._env, self._policy, self._n_envs
+        if not hasattr(pol, 'action_table'):
+            raise NotImplementedError('GridWorldEnv has discrete actions: the device path runs it with a '
+                                      'ScriptedPolicy (garage_b200.np.policies)')
+        dev = self._device()
+        gs = self._gs
+        if gs is None or gs.n != N:
+            gs = self._gs = env.grid_state(N, dev)
+        gs.reset()  # update_agent -> every env restarts (vec_worker.py:107-137)
+        table = torch.as_tensor(pol.action_table(gs.cells.numel())).to(dev)
+        L = self._max_len()
+        rows = int(math.ceil(num_samples / float(N)))
+        if L:
+            rows = int(math.ceil(rows / float(L))) * L
+        rows = max(rows, 1)
+        buf = ops.GridBuffers(rows, N, dev)
+        done_rows = 0
+        while True:
+            ops.gridworld_rollout(gs, L, table, buf, done_rows, rows - done_rows)
+            done_rows = rows
+            ws, (t_star, n_eps, n_steps, reached) = ops.pack_plan(buf.step_type[:rows], buf.ep_len[:rows], rows,
+                                                                  num_samples, sync=True)
+            if reached:
+                break
+            if n_eps == 0 and rows >= 1 << 20:
+                raise RuntimeError('no episode completes: the scripted walk never ends and there is no '
+                                   'max_episode_length')
+            more = max(L if L else 64, rows // 2)
+            old, buf = buf, ops.GridBuffers(rows + more, N, dev)
+            for name in ('obs', 'act', 'rew', 'step_type', 'last_obs', 'ep_len'):
+                getattr(buf, name)[:rows].copy_(getattr(old, name)[:rows])
+            rows += more
+        lengths, ep_off, last_obs, ep_env, ep_end = ops.pack_index(
+            buf.step_type, buf.ep_len, buf.last_obs.view(torch.float32), ws, rows, t_star, n_eps)
+        row_map = ops.pack_rowmap(buf.step_type, buf.ep_len, ep_off, t_star)
+        packed = ops.pack_fields(buf.step_type, buf.ep_len, ep_off, t_star, n_steps,
+                                 [buf.obs, buf.act, buf.rew, buf.step_type], row_map=row_map)
+        d = DeviceEpisodeBatch._Dev()
+        d.observations, d.actions, d.rewards, d.step_types = packed
+        d.logp = d.mean = d.success = None
+        d.last_observations, d.lengths = last_obs.view(torch.int32), lengths
+        d.ep_env, d.ep_end = ep_env, ep_end
+        self.total_env_steps += n_steps
+        return DeviceEpisodeBatch(env_spec=env.spec, dev=d, n_eps=n_eps, n_steps=n_steps, log_std=0.0,
+                                  tm=buf, ep_off=ep_off, t_star=t_star, row_map=row_map)
+
     def obtain_exact_episodes(self, n_eps_per_worker, agent_update, env_update=None):
         """Exactly `n_eps_per_worker` whole episodes from EVERY env copy, env-major order (reference
         local_sampler.py:168-200 with one env per worker): every env runs from `reset()` for
@@ -322,6 +380,7 @@ class GPUSampler(Sampler):
                                    norm_stats=None if es.norm_stats is None else es.norm_stats.cpu())
         state['_es'] = None
         state['_buf'] = None
+        state['_gs'] = None
         state['_t_dev'] = None
         return state
 

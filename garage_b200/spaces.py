@@ -58,3 +58,50 @@ class Box(Space):
 
     def __repr__(self):
         return 'Box{}'.format(self.shape)
+
+
+class Discrete(Space):
+    """The subset of `akro.Discrete` the GridWorld path touches: `n`, `flat_dim` (one-hot width),
+    `flatten(_n)` / `unflatten(_n)` (one-hot), `contains`, `sample`."""
+
+    def __init__(self, n):
+        self.n = int(n)
+        self.shape = ()
+        self.dtype = np.dtype(np.int64)
+
+    @property
+    def flat_dim(self):
+        return self.n
+
+    def flatten(self, x):
+        out = np.zeros(self.n)
+        out[int(x)] = 1
+        return out
+
+    def unflatten(self, x):
+        return int(np.nonzero(np.asarray(x))[0][0])
+
+    def flatten_n(self, xs):
+        xs = np.asarray(xs, dtype=np.int64).reshape(-1)
+        out = np.zeros((len(xs), self.n))
+        out[np.arange(len(xs)), xs] = 1
+        return out
+
+    def unflatten_n(self, xs):
+        return np.nonzero(np.asarray(xs))[1]
+
+    def contains(self, x):
+        x = np.asarray(x)
+        return bool(x.shape == () and x.dtype.kind in 'iu' and 0 <= int(x) < self.n)
+
+    def sample(self):
+        return int(np.random.randint(self.n))
+
+    def __eq__(self, other):
+        return isinstance(other, Discrete) and self.n == other.n
+
+    def __hash__(self):
+        return hash(('Discrete', self.n))
+
+    def __repr__(self):
+        return 'Discrete({})'.format(self.n)

@@ -111,6 +111,33 @@ int b2g_episode_stats(const void* rewards, int rewards_f64, const uint8_t* step_
                       int64_t fixed_len, double discount, int64_t n_eps, double* per_episode4,
                       double* out7, void* stream);
 
+/* ------------------------------------------------------------- GridWorld --
+ * GridWorldEnv (envs/grid_world_env.py:44-250) for N env copies of one map, and the VecWorker
+ * loop (sampler/vec_worker.py:107-219) over it with a ScriptedPolicy
+ * (np/policies/scripted_policy.py:6-60: action = scripted_actions[observation]).  Integer work:
+ * bit-exact against the reference (tests/golden/gridworld.npz).
+ * cells[n_row*n_col] u8 (device): 0 free/start, 1 wall, 2 hole, 3 goal.  state / step_cnt: int32[N]
+ * device arrays owned by the caller; step_cnt < 0 means "reset() needed" (the rollout resets such
+ * envs to start_state itself; b2g_gridworld_step reports them through err like the reference's
+ * RuntimeError, grid_world_env.py:139-140).
+ * b2g_gridworld_step == Environment.step for every env (actions int32[N] in 0..3): writes obs
+ * (next state), reward (1 at the goal), step_type (StepType codes; timeout wins over done).
+ * b2g_gridworld_rollout: n_steps rows of time-major [n_steps, N] buffers (obs = the state the
+ * action was chosen from, act, rew, step_type; last_obs / ep_len at rows that end an episode);
+ * the buffers go through b2g_pack_* unchanged (last_obs is bit-copied, O = 1). */
+#define B2G_GW_FREE 0
+#define B2G_GW_WALL 1
+#define B2G_GW_HOLE 2
+#define B2G_GW_GOAL 3
+int b2g_gridworld_step(const uint8_t* cells, int n_row, int n_col, int max_episode_length,
+                       int32_t* state, int32_t* step_cnt, const int32_t* action, int32_t* obs,
+                       float* reward, uint8_t* step_type, int32_t* err, int64_t N, void* stream);
+int b2g_gridworld_rollout(const uint8_t* cells, int n_row, int n_col, int start_state,
+                          int max_episode_length, const int32_t* scripted_actions,
+                          int32_t* state, int32_t* step_cnt, int n_steps, int64_t N, int32_t* obs,
+                          int32_t* act, float* rew, uint8_t* step_type, int32_t* last_obs,
+                          int32_t* ep_len, void* stream);
+
 /* ------------------------------------------------------------------ envs --
  * GPU-resident batched environments.  env_id selects the dynamics; `params`
  * is a HOST array of B2G_ENV_NPARAMS doubles:

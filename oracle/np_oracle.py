@@ -592,3 +592,51 @@ def pack_episodes(step_type, ep_len, num_samples, fields):
         parts = [f[t - L + 1:t + 1, n] for t, n, L in eps]
         packed.append(np.concatenate(parts) if parts else f[:0, 0])
     return lengths, packed, [(t, n) for t, n, _ in eps]
+
+
+# ------------------------------------------------------------------ GridWorld --
+GW_CODES = {'S': 0, 'F': 0, '.': 0, 'W': 1, 'x': 1, 'H': 2, 'o': 2, 'G': 3}
+
+
+def gridworld_step(cells, state, action):
+    """One transition of GridWorldEnv (reference envs/grid_world_env.py:129-176, 227-250).
+    cells: 2-D array of characters.  Returns (next_state, reward, done)."""
+    n_row, n_col = cells.shape
+    x, y = divmod(int(state), n_col)
+    dx, dy = [(0, -1), (1, 0), (0, 1), (-1, 0)][int(action)]
+    nx, ny = min(max(x + dx, 0), n_row - 1), min(max(y + dy, 0), n_col - 1)
+    here, there = GW_CODES[cells[x, y]], GW_CODES[cells[nx, ny]]
+    nxt = state if (there == 1 or here in (2, 3)) else nx * n_col + ny
+    kind = GW_CODES[cells[divmod(int(nxt), n_col)]]
+    return int(nxt), float(kind == 3), kind in (2, 3)
+
+
+def gridworld_vec_rollout(cells, table, max_episode_length, n_envs, num_samples):
+    """VecWorker + LocalSampler over n_envs copies of a GridWorldEnv with a ScriptedPolicy
+    (sampler/vec_worker.py:107-219, sampler/local_sampler.py:134-166): whole batches of lockstep
+    steps until at least num_samples steps of completed episodes exist.  Returns dict of
+    observations, actions, rewards, step_types, last_observations, lengths (episode-major, in
+    completion order, ties in env order)."""
+    start = int(np.argwhere(cells == 'S')[0] @ np.array([cells.shape[1], 1]))
+    state = [start] * n_envs
+    cnt = [0] * n_envs
+    cur = [dict(o=[], a=[], r=[], s=[]) for _ in range(n_envs)]
+    out = dict(observations=[], actions=[], rewards=[], step_types=[], last_observations=[], lengths=[])
+    total = 0
+    while total < num_samples:
+        for n in range(n_envs):
+            a = int(table[state[n]])
+            nxt, rew, done = gridworld_step(cells, state[n], a)
+            cnt[n] += 1
+            st = get_step_type(cnt[n], max_episode_length, done)
+            e = cur[n]
+            e['o'].append(state[n]); e['a'].append(a); e['r'].append(rew); e['s'].append(int(st))
+            if int(st) >= 2:
+                out['observations'] += e['o']; out['actions'] += e['a']; out['rewards'] += e['r']
+                out['step_types'] += e['s']; out['last_observations'].append(nxt); out['lengths'].append(cnt[n])
+                total += cnt[n]
+                cur[n] = dict(o=[], a=[], r=[], s=[])
+                state[n], cnt[n] = start, 0
+            else:
+                state[n] = nxt
+    return {k: np.asarray(v) for k, v in out.items()}

@@ -141,3 +141,15 @@ def test_port_train_once_matches_reference(case):
     assert abs(out['policy_loss_after'] - logs['GaussianMLPPolicy/LossAfter']) < 1e-6
     assert abs(out['vf_loss_after'] - logs['GaussianMLPValueFunction/LossAfter']) <= 1e-5 * abs(out['vf_loss_after'])
     assert abs(out['kl'] - logs['GaussianMLPPolicy/KL']) < 1e-6
+
+
+@pytest.mark.parametrize('k', range(6))
+def test_gridworld_vecworker_restatement(k):
+    """oracle.gridworld_vec_rollout vs the reference's VecWorker + LocalSampler on GridWorldEnv
+    with a ScriptedPolicy (fixture: oracle/gen_golden.py::gen_gridworld); integers, bit-exact."""
+    d = np.load(os.path.join(os.path.dirname(__file__), 'golden', 'gridworld.npz'))
+    c = {name[len('c%d_' % k):]: d[name] for name in d.files if name.startswith('c%d_' % k)}
+    got = O.gridworld_vec_rollout(c['cells'], c['table'], int(c['max_len']), int(c['n_envs']),
+                                  int(c['num_samples']))
+    for key in ('observations', 'actions', 'rewards', 'step_types', 'last_observations', 'lengths'):
+        np.testing.assert_array_equal(got[key], c[key], err_msg=key)
