@@ -338,7 +338,7 @@ class DeviceEpisodeBatch(EpisodeBatch):
     @property
     def rewards(self):
         # python floats in the reference -> float64 (Q9)
-        return self._get('rewards', lambda: self._host('rewards').astype(np.float64))
+        return self._get('rewards', lambda: self._host('rewards').astype(np.float64, copy=False))
 
     @property
     def step_types(self):
@@ -391,6 +391,10 @@ class DeviceEpisodeBatch(EpisodeBatch):
                 t = getattr(self.dev, name, None)
                 if t is None:
                     continue
+                if name == 'rewards' and t.dtype == torch.float32:
+                    # the reference's rewards are float64 (Q9): widen on the device, so the host
+                    # attribute is a view of the pinned buffer instead of an astype() pass
+                    t = t.double()
                 key = (name, tuple(t.shape), t.dtype)
                 buf = DeviceEpisodeBatch._pinned_pool.get(key)
                 if buf is None:
