@@ -167,6 +167,40 @@ class EpisodeBatch:
                    step_types=np.concatenate([b.step_types for b in batches]),
                    lengths=np.concatenate([b.lengths for b in batches]))
 
+    @classmethod
+    def from_list(cls, env_spec, paths):
+        """EpisodeBatch from a list of per-episode dicts (reference `:730-808`).  Keys per path:
+        observations (T or T+1 rows), optional next_observations, actions, rewards, step_types
+        (or legacy `dones`), env_infos, agent_infos, episode_infos.  With T+1 observation rows the
+        last row is the episode's final observation; otherwise next_observations[-1] is, and
+        failing that the last observation is duplicated (the reference's lenient fallback)."""
+        lengths = np.asarray([len(p['rewards']) for p in paths])
+        if all(len(p['observations']) == n + 1 for p, n in zip(paths, lengths)):
+            last_observations = np.asarray([p['observations'][-1] for p in paths])
+            observations = np.concatenate([p['observations'][:-1] for p in paths])
+        else:
+            observations = np.concatenate([p['observations'] for p in paths])
+            key = 'next_observations' if paths[0].get('next_observations') is not None else 'observations'
+            last_observations = np.asarray([p[key][-1] for p in paths])
+
+        def stacked(name):
+            return np.concatenate([np.asarray(p[name]) for p in paths])
+
+        if 'step_types' in paths[0]:
+            step_types = stacked('step_types')
+        elif 'dones' in paths[0]:
+            step_types = np.array([StepType.TERMINAL if d else StepType.MID for d in stacked('dones')],
+                                  dtype=StepType)
+        else:
+            raise KeyError('paths need step_types (or dones)')
+        infos = [p.get('episode_infos', {}) for p in paths]
+        episode_infos = {k: np.asarray([i[k] for i in infos]) for k in (infos[0] if infos else {})}
+        return cls(env_spec=env_spec, episode_infos=episode_infos, observations=observations,
+                   last_observations=last_observations, actions=stacked('actions'), rewards=stacked('rewards'),
+                   env_infos=_concat_nested([p['env_infos'] for p in paths]),
+                   agent_infos=_concat_nested([p['agent_infos'] for p in paths]),
+                   step_types=step_types, lengths=lengths)
+
     def _episode_ranges(self):
         stops = np.cumsum(self.lengths)
         return zip(stops - self.lengths, stops)

@@ -63,3 +63,56 @@ def test_gym_env_shim():
         GymEnv('Pendulum-v0', is_image=True)
     with pytest.raises(ValueError):
         GymEnv(object())
+
+
+def _batch():
+    from garage_b200 import EnvSpec, EpisodeBatch, StepType
+    lengths = np.array([3, 1, 2])
+    n = int(lengths.sum())
+    rng = np.random.default_rng(0)
+    st = np.array([StepType.FIRST, StepType.MID, StepType.TERMINAL, StepType.TIMEOUT, StepType.FIRST,
+                   StepType.TIMEOUT], dtype=StepType)
+    spec = EnvSpec(Box(-np.ones(3), np.ones(3)), Box(-np.ones(2), np.ones(2)), max_episode_length=3)
+    return EpisodeBatch(
+        spec, episode_infos={'goal': rng.normal(size=(3, 2))},
+        observations=rng.uniform(-1, 1, size=(n, 3)).astype(np.float32),
+        last_observations=rng.uniform(-1, 1, size=(3, 3)).astype(np.float32),
+        actions=rng.uniform(-1, 1, size=(n, 2)).astype(np.float32), rewards=rng.normal(size=n),
+        env_infos={'success': rng.random(n) < 0.5, 'task': {'id': np.arange(n)}},
+        agent_infos={'mean': rng.normal(size=(n, 2)).astype(np.float32)}, step_types=st, lengths=lengths)
+
+
+def test_episode_batch_to_list_from_list_round_trip():
+    """Reference tests/garage/test_dtypes.py: to_list() -> from_list() reproduces the batch, with
+    next_observations carrying each episode's final observation."""
+    from garage_b200 import EpisodeBatch, StepType
+    b = _batch()
+    paths = b.to_list()
+    assert [len(p['rewards']) for p in paths] == [3, 1, 2]
+    np.testing.assert_array_equal(paths[0]['next_observations'][-1], b.last_observations[0])
+    np.testing.assert_array_equal(paths[0]['next_observations'][:-1], b.observations[1:3])
+    back = EpisodeBatch.from_list(b.env_spec, paths)
+    for name in ('observations', 'last_observations', 'actions', 'rewards', 'lengths'):
+        np.testing.assert_array_equal(getattr(back, name), getattr(b, name), err_msg=name)
+    assert list(back.step_types) == list(b.step_types) and back.step_types.dtype == StepType
+    np.testing.assert_array_equal(back.env_infos['task']['id'], np.arange(6))
+    np.testing.assert_array_equal(back.agent_infos['mean'], b.agent_infos['mean'])
+    assert back.episode_infos_by_episode['goal'].shape[0] == 3
+    # T + 1 observation rows: the extra row is the final observation
+    plus = [dict(p, observations=np.concatenate([p['observations'], p['next_observations'][-1:]])) for p in paths]
+    for p in plus:
+        p.pop('next_observations')
+    again = EpisodeBatch.from_list(b.env_spec, plus)
+    np.testing.assert_array_equal(again.observations, b.observations)
+    np.testing.assert_array_equal(again.last_observations, b.last_observations)
+    # legacy `dones`, no next_observations: last observation duplicated, TERMINAL/MID step types
+    legacy = [{k: v for k, v in p.items() if k not in ('step_types', 'next_observations')} for p in paths]
+    for p, n in zip(legacy, [3, 1, 2]):
+        p['dones'] = np.array([False] * (n - 1) + [True])
+    old = EpisodeBatch.from_list(b.env_spec, legacy)
+    np.testing.assert_array_equal(old.last_observations[0], b.observations[2])
+    assert [int(s) for s in old.step_types] == [1, 1, 2, 2, 1, 2]
+    # split() / concatenate() round trip
+    cat = EpisodeBatch.concatenate(*b.split())
+    np.testing.assert_array_equal(cat.observations, b.observations)
+    np.testing.assert_array_equal(cat.lengths, b.lengths)
