@@ -156,15 +156,29 @@ class VPG(RLAlgorithm):
         ls_dev = self._log_std_dev(eps, rew_tm.device)
         if self._pad_value_mode == 'reference' and not fixed:
             return self._prepare_padded(eps, dev, ls_dev, int(self.max_episode_length), True)
-        values = vf.module.mean(tm.obs[:T].reshape(T * N, -1)).reshape(T, N)
         kw = dict(discount=self._discount, gae_lambda=self._gae_lambda)
-        if self._maximum_entropy:
-            # vpg.py:149-160: returns from the raw rewards, advantages from rewards + coeff * entropy
-            rew_ent = rew_tm + (self._policy_ent_coeff * self._entropy_value(ls_dev)).to(torch.float32)
-            adv_tm, _ = ops.gae_time_major(rew_ent, values, tm.step_type[:T], want_ret=False, **kw)
+        f.vf_before = None
+        if fixed and self._log_stats and not self._maximum_entropy:
+            # Every rollout row is in the batch, so the baselines pass can also produce the value
+            # function's LossBefore (vpg.py:170-173): returns first (they need no baselines), then ONE
+            # forward pass writes V(obs) and sums (V - return)^2, then the advantages.
             _, ret_tm = ops.gae_time_major(rew_tm, None, tm.step_type[:T], want_adv=False, **kw)
+            vals = torch.empty(T * N, 1, dtype=torch.float32, device=rew_tm.device)
+            nb = ops.mlp_eval(vf.mlp_shape, vf.flat, tm.obs[:T].reshape(T * N, -1), ret=ret_tm.reshape(-1),
+                              loss_kind=ops.LOSS_VF, mean_out=vals)
+            f.vf_before = torch.empty(8, dtype=torch.float64, device=rew_tm.device)
+            ops.mlp_reduce(vf.mlp_shape, nb, 1.0, stats_out=f.vf_before)
+            values = vals.reshape(T, N)
+            adv_tm, _ = ops.gae_time_major(rew_tm, values, tm.step_type[:T], want_ret=False, **kw)
         else:
-            adv_tm, ret_tm = ops.gae_time_major(rew_tm, values, tm.step_type[:T], **kw)
+            values = vf.module.mean(tm.obs[:T].reshape(T * N, -1)).reshape(T, N)
+            if self._maximum_entropy:
+                # vpg.py:149-160: returns from the raw rewards, advantages from rewards + coeff * entropy
+                rew_ent = rew_tm + (self._policy_ent_coeff * self._entropy_value(ls_dev)).to(torch.float32)
+                adv_tm, _ = ops.gae_time_major(rew_ent, values, tm.step_type[:T], want_ret=False, **kw)
+                _, ret_tm = ops.gae_time_major(rew_tm, None, tm.step_type[:T], want_adv=False, **kw)
+            else:
+                adv_tm, ret_tm = ops.gae_time_major(rew_tm, values, tm.step_type[:T], **kw)
         adv, ret = ops.pack_fields(tm.step_type, tm.ep_len, eps.ep_off, eps.t_star, eps.n_steps,
                                    [adv_tm, ret_tm], row_map=getattr(eps, 'row_map', None))
         f.obs, f.act, f.rew, f.ret = dev.observations, dev.actions, dev.rewards, ret
@@ -275,14 +289,18 @@ class VPG(RLAlgorithm):
                     ent_coeff=self._policy_ent_coeff, min_log_std=mod.min_log_std,
                     max_log_std=mod.max_log_std)
 
-    def _evaluate(self, f, out):
+    def _evaluate(self, f, out, vf_stats=None):
         """The logging passes of vpg.py:168-173 / 178-184 in two forward launches:
-        out[0:8] policy statistics (loss, KL(old||new), entropy sums), out[8:16] value loss."""
+        out[0:8] policy statistics (loss, KL(old||new), entropy sums), out[8:16] value loss
+        (`vf_stats`: already computed by the baselines pass, see _prepare_device)."""
         pshape, vshape = self.policy.mlp_shape, self._value_function.mlp_shape
         nb = ops.mlp_eval(pshape, self.policy.flat, f.obs, act=f.act, adv=f.adv,
                           old_logp=f.old_logp, old_mean=f.old_mean, old_log_std=f.old_log_std,
                           **self._policy_kwargs())
         ops.mlp_reduce(pshape, nb, 1.0, stats_out=out[0:8])
+        if vf_stats is not None:
+            out[8:16].copy_(vf_stats)
+            return
         nb = ops.mlp_eval(vshape, self._value_function.flat, f.obs, ret=f.ret, loss_kind=ops.LOSS_VF)
         ops.mlp_reduce(vshape, nb, 1.0, stats_out=out[8:16])
 
@@ -426,7 +444,7 @@ class VPG(RLAlgorithm):
             zero_obs = torch.zeros(1, f.obs.shape[1], device=f.obs.device)
             old_mean0 = self.policy._module.mean(zero_obs)
         if self._log_stats:
-            self._evaluate(f, stats[0:16])
+            self._evaluate(f, stats[0:16], vf_stats=getattr(f, 'vf_before', None))
         self._train(f)
         if self._log_stats:
             self._evaluate(f, stats[16:32])

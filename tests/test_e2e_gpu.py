@@ -169,3 +169,32 @@ def test_ppo_learns_point_env():
     tr.train(n_epochs=40, batch_size=512 * 40)
     first, last = tr.log[0]['Evaluation/AverageReturn'], tr.log[-1]['Evaluation/AverageReturn']
     assert last > first + 10, (first, last)
+
+
+def test_baselines_pass_also_gives_vf_loss_before():
+    """Fixed-length batches: the baselines pass doubles as the value function's LossBefore pass
+    (returns are computed first).  Advantages and returns are bit-identical to the two-pass form
+    and the statistics equal a separate evaluation on the packed batch."""
+    from garage_b200 import ops
+    from garage_b200.envs import CartPoleEnv, PendulumEnv
+    env = PendulumEnv(max_episode_length=50)
+    a, policy, vf, sampler = build(env, n_envs=256, algo='ppo', epochs=2, mb=1600)
+    eps = sampler.obtain_samples(0, 256 * 50, policy)
+    a._log_stats = True
+    merged = a._prepare_device(eps)
+    a._log_stats = False
+    plain = a._prepare_device(eps)
+    assert merged.vf_before is not None and plain.vf_before is None
+    assert torch.equal(merged.adv, plain.adv) and torch.equal(merged.ret, plain.ret)
+    out = torch.zeros(8, dtype=torch.float64, device='cuda')
+    nb = ops.mlp_eval(vf.mlp_shape, vf.flat, plain.obs, ret=plain.ret, loss_kind=ops.LOSS_VF)
+    ops.mlp_reduce(vf.mlp_shape, nb, 1.0, stats_out=out)
+    torch.testing.assert_close(merged.vf_before, out, rtol=1e-6, atol=0)
+    v, r = vf.module.mean(plain.obs).reshape(-1).double(), plain.ret.double()
+    want = (0.5 * (r - v) ** 2 + 0.5 * math.log(2 * math.pi)).sum()
+    torch.testing.assert_close(merged.vf_before[0], want, rtol=1e-6, atol=0)
+    # ragged batches (early termination) keep the separate pass
+    env2 = CartPoleEnv(max_episode_length=50)
+    a2, policy2, _, sampler2 = build(env2, n_envs=128, algo='ppo', epochs=1, mb=None)
+    f2 = a2._prepare_device(sampler2.obtain_samples(0, 128 * 50, policy2))
+    assert f2.vf_before is None
