@@ -171,7 +171,6 @@ __device__ __forceinline__ void net_loop(const NetLoop& n, int j, int ctas, uint
             cta.stamps = (n.timing && gstep == n.timing_step) ? n.tile_timing + (int64_t)j * 32 : nullptr;
             cta.stamp(0);
             cta.template run_tiles<false>(a, j, ctas);
-            cta.stamps = nullptr;
         }
         LOOP_STAMP(1);
         const float inv_mb = 1.0f / ((float)a.mb * (float)(n.world > 1 ? n.world : 1));  // the minibatch spans all ranks
@@ -190,6 +189,7 @@ __device__ __forceinline__ void net_loop(const NetLoop& n, int j, int ctas, uint
             pp = __ldcg(n.params + pidx);
         }
         cta.write_partial(out, false);
+        cta.stamps = nullptr;
         LOOP_STAMP(2);
         net_barrier(n.sync, ++nbar * (unsigned int)ctas);
         LOOP_STAMP(3);

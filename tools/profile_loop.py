@@ -86,6 +86,9 @@ def main():
             print('--- net', k, 'after tiles: set_step {:.0f}, prime {:.0f}, rest until partial written {:.0f}'.format(
                 np.median(t[k][:, 8] - t[k][:, 1]), np.median(t[k][:, 9] - t[k][:, 8]), np.median(t[k][:, 2] - t[k][:, 9])))
         for k in range(len(nets)):
+            print('--- net', k, 'stamp 9 -> write_partial entry {:.0f}, write_partial exit -> stamp 2 {:.0f}'.format(
+                np.median(tiles[k][:, 28] - t[k][:, 9]), np.median(t[k][:, 2] - tiles[k][:, 30])))
+        for k in range(len(nets)):
             tt = tiles[k]
             print('--- net', k, 'write_partial: drain wait {:.0f}, TMEM->smem->global {:.0f} (median cycles)'.format(
                 np.median(tt[:, 29] - tt[:, 28]), np.median(tt[:, 30] - tt[:, 29])))
