@@ -15,6 +15,16 @@
 #include "envs.cuh"
 #include "mlp.cuh"
 
+// tanh x = 1 - 2 / (1 + e^{2x}) on the SFU (ex2 / rcp), absolute error ~2e-7: the same activation
+// the tensor-core update kernels evaluate (mlp_tc.cuh), a quarter of tanhf's instructions.  The
+// rollout is serial over time with ~8 warps per SM, so instruction count is what it pays for.
+__device__ __forceinline__ float ro_tanh(float x) {
+    float e, r;
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e) : "f"(x * 2.8853900817779268f));
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(e + 1.0f));
+    return fmaf(-2.0f, r, 1.0f);
+}
+
 struct RolloutArgs {
     EnvParams P;
     NormParams Q;        // normalize(env) wrapper (envs.cuh); used by the NORM instantiations only
@@ -126,7 +136,7 @@ rollout_kernel(const RolloutArgs a) {
                 float z = b1[u];
 #pragma unroll
                 for (int i = 0; i < O; ++i) z = fmaf(w1[u][i], x[g][i], z);
-                sh_h[wib][g][lane + 32 * u] = tanhf(z);
+                sh_h[wib][g][lane + 32 * u] = ro_tanh(z);
             }
         __syncwarp();
         // ---- layer 2: h2 = tanh(W2 h1 + b2); h1 re-read as broadcast float4
@@ -158,7 +168,7 @@ rollout_kernel(const RolloutArgs a) {
             for (int q = 0; q < A; ++q) {
                 float p = 0.0f;
 #pragma unroll
-                for (int u = 0; u < UPL; ++u) p = fmaf(w3[q][u], tanhf(acc[g][u]), p);
+                for (int u = 0; u < UPL; ++u) p = fmaf(w3[q][u], ro_tanh(acc[g][u]), p);
 #pragma unroll
                 for (int o = 16; o > 0; o >>= 1) p += __shfl_xor_sync(0xffffffffu, p, o);
                 m[g][q] = p + b3[q];
