@@ -289,15 +289,23 @@ class VPG(RLAlgorithm):
                     ent_coeff=self._policy_ent_coeff, min_log_std=mod.min_log_std,
                     max_log_std=mod.max_log_std)
 
-    def _evaluate(self, f, out, vf_stats=None):
+    def _evaluate(self, f, out, vf_stats=None, before=False):
         """The logging passes of vpg.py:168-173 / 178-184 in two forward launches:
         out[0:8] policy statistics (loss, KL(old||new), entropy sums), out[8:16] value loss
         (`vf_stats`: already computed by the baselines pass, see _prepare_device)."""
         pshape, vshape = self.policy.mlp_shape, self._value_function.mlp_shape
-        nb = ops.mlp_eval(pshape, self.policy.flat, f.obs, act=f.act, adv=f.adv,
-                          old_logp=f.old_logp, old_mean=f.old_mean, old_log_std=f.old_log_std,
-                          **self._policy_kwargs())
-        ops.mlp_reduce(pshape, nb, 1.0, stats_out=out[0:8])
+        if before and self._loss_kind == ops.LOSS_PPO and self._entropy_method == 'no_entropy':
+            # Before the update the reference's old policy IS the policy (ppo.py:96-132 with
+            # vpg.py:168-173: deepcopy, re-synchronised after every _train_once), so the likelihood
+            # ratio is exactly 1 on every row: LossBefore = -mean(advantages), KLBefore = 0 -- no
+            # forward pass needed (out is zero-initialised; only [0] and [1] of the "before" block
+            # are logged).
+            out[0] = -f.adv.sum(dtype=torch.float64)
+        else:
+            nb = ops.mlp_eval(pshape, self.policy.flat, f.obs, act=f.act, adv=f.adv,
+                              old_logp=f.old_logp, old_mean=f.old_mean, old_log_std=f.old_log_std,
+                              **self._policy_kwargs())
+            ops.mlp_reduce(pshape, nb, 1.0, stats_out=out[0:8])
         if vf_stats is not None:
             out[8:16].copy_(vf_stats)
             return
@@ -444,7 +452,7 @@ class VPG(RLAlgorithm):
             zero_obs = torch.zeros(1, f.obs.shape[1], device=f.obs.device)
             old_mean0 = self.policy._module.mean(zero_obs)
         if self._log_stats:
-            self._evaluate(f, stats[0:16], vf_stats=getattr(f, 'vf_before', None))
+            self._evaluate(f, stats[0:16], vf_stats=getattr(f, 'vf_before', None), before=True)
         self._train(f)
         if self._log_stats:
             self._evaluate(f, stats[16:32])

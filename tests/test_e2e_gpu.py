@@ -198,3 +198,29 @@ def test_baselines_pass_also_gives_vf_loss_before():
     a2, policy2, _, sampler2 = build(env2, n_envs=128, algo='ppo', epochs=1, mb=None)
     f2 = a2._prepare_device(sampler2.obtain_samples(0, 128 * 50, policy2))
     assert f2.vf_before is None
+
+
+def test_ppo_loss_before_without_forward_pass():
+    """Before the update the likelihood ratio is 1 on every row (the reference's old policy is a
+    synchronised copy), so PPO's LossBefore is -mean(adv) and KLBefore 0; the forward-pass form
+    agrees to rounding.  VPG and entropy-regularised PPO keep the forward pass."""
+    from garage_b200.envs import PendulumEnv
+    env = PendulumEnv(max_episode_length=40)
+    a, policy, vf, sampler = build(env, n_envs=128, algo='ppo', epochs=1, mb=None)
+    f = a._prepare_device(sampler.obtain_samples(0, 128 * 40, policy))
+    fast = torch.zeros(16, dtype=torch.float64, device='cuda')
+    full = torch.zeros(16, dtype=torch.float64, device='cuda')
+    a._evaluate(f, fast, before=True)
+    a._evaluate(f, full, before=False)
+    B = float(f.B)
+    assert abs(fast[0].item() / B - full[0].item() / B) < 1e-6
+    assert fast[1].item() == 0.0 and abs(full[1].item() / B) < 1e-9   # KL(old || new)
+    torch.testing.assert_close(fast[8:16], full[8:16])                # value-function block untouched
+    torch.testing.assert_close(fast[0], -f.adv.sum(dtype=torch.float64))
+    v, _, _, s2 = build(env, n_envs=128, algo='vpg', epochs=1, mb=None)
+    fv = v._prepare_device(s2.obtain_samples(0, 128 * 40, v.policy))
+    o1 = torch.zeros(16, dtype=torch.float64, device='cuda')
+    o2 = torch.zeros(16, dtype=torch.float64, device='cuda')
+    v._evaluate(fv, o1, before=True)
+    v._evaluate(fv, o2, before=False)
+    assert torch.equal(o1, o2) and o1[2].item() != 0.0  # same forward pass either way (entropy sum present)
