@@ -102,6 +102,7 @@ class GPUSampler(Sampler):
         self._t_dev = None  # device-side global step counter (Philox counter word)
         self._es = None
         self._gs = None  # GridWorld device state (GridWorldEnv + ScriptedPolicy path)
+        self._static_pack = None  # (shape key, row statistics, row map) of a never-terminating env
         self._buf = None
         self.total_env_steps = 0
 
@@ -165,6 +166,7 @@ class GPUSampler(Sampler):
             self._env = env_update
             self._es = None
             self._buf = None
+            self._static_pack = None
 
     # -------------------------------------------------------------------- API --
     def obtain_samples(self, itr, num_samples, agent_update, env_update=None):
@@ -195,6 +197,7 @@ class GPUSampler(Sampler):
         rows = max(rows, 1)
         self._ensure_buffers(rows)
         done_rows = 0
+        cached = key = None
         while True:
             ops.rollout(self._es, prm, L, pol.flat, pol.mlp_shape.H, pol._module.min_log_std,
                         self._max_log_std(), self._seed, self._env_id_offset, 0,
@@ -202,8 +205,13 @@ class GPUSampler(Sampler):
             ops.counter_add(self._t_dev, rows - done_rows)
             done_rows = rows
             if static:
+                # never-terminating env: every episode is exactly L steps, so the episode structure
+                # (row statistics, packed row of every step) depends on the shape alone -- planned
+                # once per shape and reused; only the field data is packed every call
                 t_star, n_eps, n_steps = rows - 1, N * (rows // L), N * rows
-                ws, _ = self._plan(rows, num_samples, sync=False)
+                key = (env.env_id, rows, N, L, int(num_samples), str(self._device()))
+                cached = self._static_pack if self._static_pack and self._static_pack[0] == key else None
+                ws = cached[1] if cached else self._plan(rows, num_samples, sync=False)[0]
                 break
             ws, (t_star, n_eps, n_steps, reached) = self._plan(rows, num_samples, sync=True)
             if reached:
@@ -218,7 +226,10 @@ class GPUSampler(Sampler):
                 if src is not None:
                     getattr(self._buf, name)[:rows].copy_(src[:rows])
             rows += more
-        batch = self._pack(ws, rows, t_star, n_eps, n_steps, static)
+        batch = self._pack(ws, rows, t_star, n_eps, n_steps, static,
+                           row_map=cached[2] if static and cached else None)
+        if static and not cached:
+            self._static_pack = (key, ws, batch.row_map)
         self.total_env_steps += n_steps
         return batch
 
@@ -226,7 +237,7 @@ class GPUSampler(Sampler):
         b = self._buf
         return ops.pack_plan(b.step_type[:rows], b.ep_len[:rows], rows, num_samples, sync=sync)
 
-    def _pack(self, ws, rows, t_star, n_eps, n_steps, static):
+    def _pack(self, ws, rows, t_star, n_eps, n_steps, static, row_map=None):
         b, env, pol = self._buf, self._env, self._policy
         lengths, ep_off, last_obs, ep_env, ep_end = ops.pack_index(
             b.step_type, b.ep_len, b.last_obs, ws, rows, t_star, n_eps)
@@ -235,7 +246,8 @@ class GPUSampler(Sampler):
             fields.append(b.mean)
         if b.success is not None:
             fields.append(b.success)
-        row_map = ops.pack_rowmap(b.step_type, b.ep_len, ep_off, t_star)
+        if row_map is None:
+            row_map = ops.pack_rowmap(b.step_type, b.ep_len, ep_off, t_star)
         packed = ops.pack_fields(b.step_type, b.ep_len, ep_off, t_star, n_steps, fields, row_map=row_map)
         dev = DeviceEpisodeBatch._Dev()
         dev.observations, dev.actions, dev.rewards, dev.logp, dev.step_types = packed[:5]
@@ -368,6 +380,7 @@ class GPUSampler(Sampler):
         """Nothing to shut down: there are no worker processes."""
         self._es = None
         self._buf = None
+        self._static_pack = None
 
     def __getstate__(self):
         """cloudpickle-able: device buffers are rebuilt lazily; what identifies the position in the
@@ -381,6 +394,7 @@ class GPUSampler(Sampler):
         state['_es'] = None
         state['_buf'] = None
         state['_gs'] = None
+        state['_static_pack'] = None
         state['_t_dev'] = None
         return state
 

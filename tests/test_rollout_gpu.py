@@ -191,3 +191,30 @@ def test_rollout_independent_of_sharding():
     full, a, b = run(N, 0), run(N // 2, 0), run(N // 2, N // 2)
     for k in ('obs', 'act', 'rew', 'logp', 'step_type'):
         assert torch.equal(getattr(full, k), torch.cat([getattr(a, k), getattr(b, k)], dim=1)), k
+
+
+def test_static_pack_plan_is_reused_without_changing_the_batch():
+    """Never-terminating envs: the pack plan / row map of a shape is computed once and reused; the
+    second batch equals the one a sampler without the cached plan produces, and a different
+    num_samples (another shape) re-plans."""
+    from garage_b200.envs import PendulumEnv
+    from garage_b200.sampler import GPUSampler
+    from garage_b200.torch.policies import GaussianMLPPolicy
+    env = PendulumEnv(max_episode_length=25)
+    torch.manual_seed(4)
+    pol = GaussianMLPPolicy(env.spec, hidden_sizes=(64, 64))
+    a = GPUSampler(pol, env, max_episode_length=25, n_envs=96, seed=9)
+    b = GPUSampler(pol, env, max_episode_length=25, n_envs=96, seed=9)
+    a.obtain_samples(0, 96 * 25, pol)
+    b.obtain_samples(0, 96 * 25, pol)
+    assert a._static_pack is not None
+    map_before = a._static_pack[2]
+    b._static_pack = None                      # b plans again, a reuses
+    ea, eb = a.obtain_samples(1, 96 * 25, pol), b.obtain_samples(1, 96 * 25, pol)
+    assert a._static_pack[2] is map_before and ea.row_map is map_before
+    for name in ('observations', 'actions', 'rewards', 'logp', 'step_types', 'mean', 'last_observations',
+                 'lengths', 'ep_env', 'ep_end'):
+        assert torch.equal(getattr(ea.dev, name), getattr(eb.dev, name)), name
+    assert torch.equal(ea.row_map, eb.row_map)
+    e2 = a.obtain_samples(2, 96 * 50, pol)    # two episodes per env: another shape
+    assert a._static_pack[2] is not map_before and e2.n_episodes == 192 and list(e2.lengths[:3]) == [25] * 3
