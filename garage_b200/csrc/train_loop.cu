@@ -47,43 +47,74 @@ struct LoopArgs {
 
 constexpr int COMM_P = 4608;  // per-network capacity of the exchange area (parameters)
 
-// One exchange slot = {value bits, step sequence number} in ONE 8-byte word: an aligned 8-byte store
-// arrives whole at the peer, so the sequence number doubles as the "data ready" flag and no
-// system-scope fence (a multi-microsecond drain of every outstanding NVLink write) is needed.
+// One exchange slot = {value bits, step sequence number} packed into ONE 64-bit word and moved with a
+// single scalar 8-byte store / load (the PTX memory model treats the halves of a .v2 access as two
+// independent accesses in unspecified order; a scalar b64 access is single-copy atomic), so the
+// sequence number doubles as the "data ready" flag and no system-scope fence (a multi-microsecond
+// drain of every outstanding NVLink write) is needed.
 __device__ __forceinline__ void st_slot(unsigned long long* p, float v, unsigned int seq) {
-    asm volatile("st.relaxed.sys.global.v2.b32 [%0], {%1, %2};" ::"l"(p), "r"(__float_as_uint(v)), "r"(seq) : "memory");
+    const unsigned long long word = ((unsigned long long)seq << 32) | (unsigned long long)__float_as_uint(v);
+    asm volatile("st.relaxed.sys.global.b64 [%0], %1;" ::"l"(p), "l"(word) : "memory");
 }
-__device__ __forceinline__ bool ld_slot(const unsigned long long* p, unsigned int seq, float& v) {
-    unsigned int lo, hi;
-    asm volatile("ld.relaxed.sys.global.v2.b32 {%0, %1}, [%2];" : "=r"(lo), "=r"(hi) : "l"(p) : "memory");
-    v = __uint_as_float(lo);
-    return hi == seq;
+__device__ __forceinline__ unsigned long long ld_slot(const unsigned long long* p) {
+    unsigned long long word;
+    asm volatile("ld.relaxed.sys.global.b64 %0, [%1];" : "=l"(word) : "l"(p) : "memory");
+    return word;
 }
+__device__ __forceinline__ unsigned long long global_ns() {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    return t;
+}
+// A peer that never answers must surface as an error, not as a hung GPU -- but ordinary host skew
+// between ranks (a snapshot on rank 0, first-call IPC mapping, a slow log disk) must not kill the
+// context: the limit is wall time (globaltimer), 120 s unless B2G_PEER_TIMEOUT_S says otherwise.
+__device__ unsigned long long g_peer_timeout_ns = 120ull * 1000000000ull;
 
 // All-reduce of one CTA's parameter slice over the ranks, inside the kernel (warp 0 of the CTA):
 // every rank stores {slice sum, seq} into every other rank's receive area over NVLink (peer-mapped
 // memory), polls its own area until the slots of all source ranks carry this step's seq, and adds
-// the contributions in rank order -- every rank obtains the same bits.  The receive area is
-// double-buffered on the step parity: a slot of step s is rewritten at step s+2, which its writer
-// can only reach after the reader's whole network passed the barrier of step s+1, i.e. after the
-// reader consumed step s.
+// the contributions in rank order -- every rank obtains the same bits.  All polls are issued
+// together (one load per source rank in flight, re-issued only for the ranks still missing), so the
+// wait is one NVLink latency plus the slowest rank's skew instead of a chain of serial round trips.
+// The receive area is double-buffered on the step parity: a slot of step s is rewritten at step
+// s+2, which its writer can only reach after the reader's whole network passed the barrier of step
+// s+1, i.e. after the reader consumed step s.
 __device__ __forceinline__ float slice_allreduce(const NetLoop& n, bool own, int pidx, float tot, unsigned int seq) {
     if (!own) return 0.0f;
     const int par = (int)(seq & 1u);
     for (int r = 0; r < n.world; ++r)
         if (r != n.rank) st_slot(n.peer_recv[r] + ((size_t)(n.rank * 2 + par) * COMM_P + pidx), tot, seq);
-    float sum = 0.0f;
-    for (int r = 0; r < n.world; ++r) {
-        float v = tot;
-        if (r != n.rank) {
-            const unsigned long long* slot = n.peer_recv[n.rank] + ((size_t)(r * 2 + par) * COMM_P + pidx);
-            unsigned int spin = 0;
-            while (!ld_slot(slot, seq, v)) {
-                if (++spin > (1u << 24)) __trap();  // a lost rank must surface as an error, not as a hung GPU
-            }
-        }
-        sum += v;
+    float v[B2G_MAX_RANKS];
+    unsigned int missing = 0;
+#pragma unroll
+    for (int r = 0; r < B2G_MAX_RANKS; ++r) {
+        v[r] = (r == n.rank) ? tot : 0.0f;
+        if (r < n.world && r != n.rank) missing |= 1u << r;
     }
+    const unsigned long long* base = n.peer_recv[n.rank] + ((size_t)par * COMM_P + pidx);
+    unsigned long long t0 = 0;
+    for (unsigned int spin = 0; missing; ++spin) {
+        unsigned long long wd[B2G_MAX_RANKS];
+#pragma unroll
+        for (int r = 0; r < B2G_MAX_RANKS; ++r)  // every outstanding poll in flight before any is examined
+            wd[r] = (missing & (1u << r)) ? ld_slot(base + (size_t)r * 2 * COMM_P) : 0ull;
+#pragma unroll
+        for (int r = 0; r < B2G_MAX_RANKS; ++r)
+            if ((missing & (1u << r)) && (unsigned int)(wd[r] >> 32) == seq) {
+                v[r] = __uint_as_float((unsigned int)wd[r]);
+                missing &= ~(1u << r);
+            }
+        if ((spin & 0xfffu) == 0xfffu) {
+            const unsigned long long now = global_ns();
+            if (t0 == 0) t0 = now;
+            else if (now - t0 > g_peer_timeout_ns) __trap();
+        }
+    }
+    float sum = 0.0f;
+#pragma unroll
+    for (int r = 0; r < B2G_MAX_RANKS; ++r)
+        if (r < n.world) sum += v[r];
     return sum;
 }
 
@@ -372,6 +403,16 @@ extern "C" int b2g_mlp_train_loop_dist(const b2g_train_net* nets, int n_nets, co
         for (int r = 0; r < comm->world; ++r) B2G_CHECK_ARG(comm->peer_base[r] != nullptr, "NULL peer buffer");
     }
     cudaStream_t s = (cudaStream_t)stream;
+    if (comm && comm->world > 1) {
+        static bool timeout_set = false;
+        if (!timeout_set) {
+            const char* e = getenv("B2G_PEER_TIMEOUT_S");
+            const double sec = e ? atof(e) : 120.0;
+            const unsigned long long ns = (unsigned long long)((sec > 0.001 ? sec : 0.001) * 1e9);
+            B2G_CUDA(cudaMemcpyToSymbol(g_peer_timeout_ns, &ns, sizeof(ns)));
+            timeout_set = true;
+        }
+    }
     const int grid = 2 * b2g_sm_count();
     LoopArgs args{};
     args.n_nets = n_nets;

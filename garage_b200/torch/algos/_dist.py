@@ -41,22 +41,34 @@ def shard_envs(n_envs_total, rank, world):
     return n, off
 
 
-def reduce_logs(s, B, group=None):
-    """Sum the loss/KL/entropy statistics and the sample count over ranks; average the
-    per-rank return means (equal shard sizes), max/min the extremes.  `s`: float64 tensor
-    [>=40] laid out like VPG._enqueue_iteration's stats; returns (s, B) tensors."""
+def reduce_logs(s, B, n_eps=None, group=None):
+    """The logging scalars of one iteration over all ranks, equal to what the reference's
+    log_performance (_functions.py:233-275) reports for the union of the shards: sums for the
+    loss / KL / entropy statistics and the sample count; the return statistics are combined from
+    per-rank (n_eps, mean, population std) -- episode-count weighted means, the GLOBAL standard
+    deviation (Chan's pairwise formula, not a mean of per-rank stds), max / min of the extremes.
+    `s`: float64 tensor [>=40] laid out like VPG._enqueue_iteration's stats (s[32:39] = mean
+    discounted return, mean / std / max / min return, termination rate, success rate).
+    Returns (s[:40] reduced, B total, n_eps total) as tensors."""
     world = world_size(group)
-    t = torch.cat([s[:40], torch.full((1,), float(B), dtype=torch.float64, device=s.device)])
+    n = float(n_eps) if n_eps is not None else 1.0
+    dd = dict(dtype=torch.float64, device=s.device)
     if world == 1:
-        return t[:-1], t[-1]
-    perf = t[32:39].clone()
+        return s[:40], torch.full((), float(B), **dd), torch.full((), n, **dd)
+    perf = s[32:39]
+    mean, std = perf[1], perf[2]
+    # [0:32] sums | n_eps | n*disc | n*mean | n*(std^2 + mean^2) | n*term | n*succ | pad (s[39]) | B
+    w = torch.stack([torch.full((), n, **dd), n * perf[0], n * mean, n * (std * std + mean * mean),
+                     n * perf[5], n * perf[6], s[39], torch.full((), float(B), **dd)])
+    t = torch.cat([s[:32], w])
     dist.all_reduce(t, group=group)
-    t[32:39] = t[32:39] / world
-    mx, mn = perf[3:4].clone(), perf[4:5].clone()
-    dist.all_reduce(mx, op=dist.ReduceOp.MAX, group=group)
-    dist.all_reduce(mn, op=dist.ReduceOp.MIN, group=group)
-    t[35], t[36] = mx[0], mn[0]
-    return t[:-1], t[-1]
+    ext = torch.stack([perf[3], -perf[4]])
+    dist.all_reduce(ext, op=dist.ReduceOp.MAX, group=group)
+    nt = t[32]
+    gmean = t[34] / nt
+    gstd = torch.sqrt(torch.clamp(t[35] / nt - gmean * gmean, min=0.0))
+    out = torch.cat([t[:32], torch.stack([t[33] / nt, gmean, gstd, ext[0], -ext[1], t[36] / nt, t[37] / nt, t[38]])])
+    return out, t[39], nt
 
 
 class PeerComm:

@@ -38,12 +38,15 @@ class _Flat:
 class VPG(RLAlgorithm):
     """See the reference docstring (vpg.py:19-55) for the shared arguments.
 
-    Extra keyword-only arguments (all have defaults that keep the reference's behaviour):
+    Extra keyword-only arguments.  The defaults reproduce the reference for fixed-length batches;
+    for batches with early-terminated episodes the default `pad_value_mode='mask'` is a DELIBERATE
+    deviation (see below) and `pad_value_mode='reference'` is the bit-for-bit parity mode:
         shuffle (str): 'device' (counter-based Feistel permutation kernel) or 'numpy'
             (np.random.shuffle on the host exactly like BatchDataset -- parity mode).
-        pad_value_mode (str): 'mask' cuts GAE at episode ends (what the reference's
-            docstring describes); 'reference' reproduces quirk Q5 (baselines evaluated on
-            zero-padded observations leak V(0) into early-terminated episodes).
+        pad_value_mode (str): 'mask' (default) cuts GAE at episode ends (what the reference's
+            docstring describes, NOT what its code computes for ragged batches); 'reference'
+            reproduces quirk Q5 (baselines evaluated on zero-padded observations leak V(0) into
+            early-terminated episodes) and is what the golden `train_once` fixtures use.
         process_group: torch.distributed group for the gradient all-reduce (default: the
             world group when torch.distributed is initialised with world_size > 1).
         update_mode (str): 'fused' runs every minibatch step of `_train` (both networks) in one
@@ -322,16 +325,34 @@ class VPG(RLAlgorithm):
                                device=self.policy.flat.device)
 
     def _run_minibatches(self, opt, module_owner, f, policy):
-        """`for epoch: for minibatch: zero_grad; loss; backward; step` (vpg.py:244-293)."""
+        """`for epoch: for minibatch: zero_grad; loss; backward; step` (vpg.py:244-293).
+
+        Several ranks: `minibatch_size` is the GLOBAL size.  Shards may differ in length (envs that
+        terminate early), but every rank must issue the same collectives, so all ranks run the same
+        number S of steps per epoch (from the longest shard) and rank r contributes ceil(B_r / S) of
+        its rows to each; the gradient of a step is the mean over the union of the ranks' rows."""
         shape, flat = module_owner.mlp_shape, module_owner.flat
         m, v, step = opt.state()
         B = f.B
         mbs = opt.minibatch_size or B
         world = self._world()
+        counts = None
         if world > 1:
             import torch.distributed as dist
-            mbs = max(1, mbs // world)  # minibatch_size is the global size
             grad = torch.empty(shape.P, dtype=torch.float32, device=flat.device)
+            bmax = torch.tensor([B], dtype=torch.int64, device=flat.device)
+            dist.all_reduce(bmax, op=dist.ReduceOp.MAX, group=self._pg)
+            bmax = int(bmax.item())
+            per_rank = max(1, (opt.minibatch_size // world) if opt.minibatch_size else bmax)
+            S = -(-bmax // per_rank)
+            mbs = -(-B // S)
+            local = [max(0, min(mbs, B - s * mbs)) for s in range(S)]
+            counts = torch.tensor(local, dtype=torch.int64, device=flat.device)
+            dist.all_reduce(counts, group=self._pg)
+            counts = counts.tolist()
+            starts = [s * mbs for s in range(S)]
+        else:
+            starts = list(range(0, B, mbs))
         host_ids = None
         if self._shuffle == 'numpy' and opt.minibatch_size is not None:
             # BatchDataset: ids shuffled at construction and AFTER every epoch, the last one
@@ -342,15 +363,20 @@ class VPG(RLAlgorithm):
         data = dict(act=f.act, adv=f.adv, old_logp=f.old_logp) if policy else dict(ret=f.ret)
         for _ in range(opt.max_optimization_epochs):
             idx = self._epoch_ids(B, opt, host_ids, step)
-            for start in range(0, B, mbs):
-                mb = min(mbs, B - start)
-                nb = ops.mlp_minibatch_grad(
-                    shape, flat, f.obs, idx=None if idx is None else idx[start:start + mb],
-                    start=start if idx is None else 0, mb=mb, step_counter=step, **data, **kw)
+            for si, start in enumerate(starts):
+                mb = max(0, min(mbs, B - start))
+                if mb > 0:
+                    nb = ops.mlp_minibatch_grad(
+                        shape, flat, f.obs, idx=None if idx is None else idx[start:start + mb],
+                        start=start if idx is None else 0, mb=mb, step_counter=step, **data, **kw)
                 if world > 1:
-                    ops.mlp_reduce(shape, nb, 1.0, grad_out=grad)
+                    if mb > 0:
+                        ops.mlp_reduce(shape, nb, 1.0, grad_out=grad)
+                    else:  # this shard is exhausted: it still joins the collective and counts the step
+                        grad.zero_()
+                        ops.counter_add(step, 1)
                     dist.all_reduce(grad, group=self._pg)
-                    ops.adam_step(flat, grad, 1.0 / (mb * world), m, v, step, opt.lr, opt.beta1,
+                    ops.adam_step(flat, grad, 1.0 / counts[si], m, v, step, opt.lr, opt.beta1,
                                   opt.beta2, opt.eps)
                 else:
                     ops.mlp_reduce(shape, nb, 1.0 / mb, params=flat, adam_m=m, adam_v=v,
@@ -403,13 +429,20 @@ class VPG(RLAlgorithm):
                 # every rank must run the same number of steps: the minibatch size is global, the
                 # shards must be equally long (fixed-length episodes); otherwise step-wise + NCCL
                 import torch.distributed as dist
-                if f.fixed_len and self._dist_B == f.B:
-                    same = True  # fixed-length batches of the size every rank agreed on before
+                # The decision must be the same on every rank (a rank that skips this all_reduce while
+                # another issues it deadlocks the job): the shortcut is taken only for envs that never
+                # terminate -- a property of the env class, identical on all ranks, under which the
+                # batch size is fixed by the configuration -- and never from what one rank's own
+                # batch happened to look like (CartPole / PointEnv shards can be full-length on one
+                # rank and ragged on another).
+                static = bool(getattr(getattr(self._sampler, '_env', None), 'never_terminates', False))
+                if static and self._dist_B == f.B:
+                    same = True  # the size every rank agreed on before
                 else:
                     b = torch.tensor([f.B, -f.B], dtype=torch.int64, device=f.obs.device)
                     dist.all_reduce(b, op=dist.ReduceOp.MAX, group=self._pg)
                     same = int(b[0]) == -int(b[1])
-                    self._dist_B = f.B if same else None
+                    self._dist_B = f.B if (same and static) else None
                 if not same:
                     if self._update_mode == 'fused':
                         raise NotImplementedError("update_mode='fused' needs equally long shards on every rank")
@@ -481,7 +514,7 @@ class VPG(RLAlgorithm):
         B = float(B)
         world = self._world()
         if world > 1:
-            s, B = self._reduce_logs(s, B, world)
+            s, B, n_eps = self._reduce_logs(s, B, n_eps, world)
         pol_before, vf_before = s[0] / B, s[8] / B
         pol_after, vf_after = s[16] / B, s[24] / B
         with tabular.prefix(self.policy.name):
@@ -511,11 +544,13 @@ class VPG(RLAlgorithm):
         self._episode_reward_mean.append(s[33])
         return np.float64(s[33])
 
-    def _reduce_logs(self, s, B, world):
-        """Logging scalars over ranks (sums for the statistics, mean/max/min for returns)."""
+    def _reduce_logs(self, s, B, n_eps, world):
+        """Logging scalars over ranks: what the reference would log for the union of the shards
+        (_dist.reduce_logs: sums, episode-weighted means, the global std, max / min)."""
         t = torch.tensor(s, dtype=torch.float64, device=self.policy.flat.device)
-        red, Bt = _dist.reduce_logs(t, B, self._pg)
-        return np.concatenate([red.cpu().numpy(), s[40:]]), float(Bt.item())
+        red, Bt, nt = _dist.reduce_logs(t, B, n_eps, self._pg)
+        # s[40:48] (KL at the zero-padded observation) depends on the parameters only: same on every rank
+        return np.concatenate([red.cpu().numpy(), s[40:]]), float(Bt.item()), int(round(float(nt.item())))
 
     def train(self, trainer):
         """Reference vpg.py:208-228."""
