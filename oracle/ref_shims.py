@@ -25,6 +25,8 @@ import types
 import numpy as np
 
 REFERENCE_SRC = '/root/reference/src'
+# staged copy of the unmodified package (oracle/make_ref.py; git-ignored, travels with gpurun)
+STAGED_SRC = os.path.join(os.path.dirname(os.path.abspath(__file__)), '_ref')
 
 _STUB_ROOTS = ('dowel', 'gym', 'ray', 'tensorflow', 'tensorflow_probability',
                'cma', 'skimage', 'mujoco_py', 'dm_control', 'metaworld',
@@ -209,8 +211,17 @@ _installed = False
 tabular = Tabular()
 
 
+def source_dir():
+    """Directory holding the reference's `garage` package: the reference tree itself in the
+    build container, the staged copy on the GPU box; None when neither exists."""
+    for d in (REFERENCE_SRC, STAGED_SRC):
+        if os.path.isdir(os.path.join(d, 'garage')):
+            return d
+    return None
+
+
 def available():
-    return os.path.isdir(os.path.join(REFERENCE_SRC, 'garage'))
+    return source_dir() is not None
 
 
 def install():
@@ -225,7 +236,8 @@ def install():
     sys.modules['dowel'].tabular = tabular
     sys.modules['dowel'].logger = _Anything()
     sys.modules['akro'] = _make_akro()
-    if REFERENCE_SRC not in sys.path:
-        sys.path.insert(0, REFERENCE_SRC)
+    src = source_dir()
+    if src not in sys.path:
+        sys.path.insert(0, src)
     _installed = True
     return True
