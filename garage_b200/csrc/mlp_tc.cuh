@@ -195,17 +195,20 @@ __device__ __forceinline__ void issue_gemm1(uint32_t sb, uint32_t tmem) {
                       umma_desc(sb + bo + (ks >> 2) * WPANEL + (ks & 3) * 32, 1024, 512), ID, (pass | ks) != 0);
     }
 }
-__device__ __forceinline__ void issue_gemm2(uint32_t sb, uint32_t tmem) {
+// MMAs [lo, hi) of the 24 (pass-major: hi*hi, lo*hi, hi*lo; 8 K steps each): the issuing lane is held
+// back while the tensor pipe's queue is full, so the caller interleaves chunks with its other work
+template <int LO, int HI>
+__device__ __forceinline__ void issue_gemm2_part(uint32_t sb, uint32_t tmem) {
     constexpr uint32_t ID = umma_idesc(64, 64, 0, 1);
 #pragma unroll
-    for (int pass = 0; pass < 3; ++pass) {
+    for (int m = LO; m < HI; ++m) {
+        const int pass = m >> 3, ks = m & 7;
         const uint32_t ao = OFF_DZ + (pass == 1 ? 2 * PANEL : 0), bo = OFF_W + (pass == 2 ? 2 * WPANEL : 0);
-#pragma unroll
-        for (int ks = 0; ks < 8; ++ks)
-            umma_tf32(tmem + TM_D, umma_desc(sb + ao + (ks >> 2) * PANEL + (ks & 3) * 32, 1024, 512),
-                      umma_desc(sb + bo + ks * 1024, WPANEL, 512), ID, (pass | ks) != 0);
+        umma_tf32(tmem + TM_D, umma_desc(sb + ao + (ks >> 2) * PANEL + (ks & 3) * 32, 1024, 512),
+                  umma_desc(sb + bo + ks * 1024, WPANEL, 512), ID, m != 0);
     }
 }
+__device__ __forceinline__ void issue_gemm2(uint32_t sb, uint32_t tmem) { issue_gemm2_part<0, 24>(sb, tmem); }
 // nks = ceil(valid rows / 8): rows past the minibatch contribute nothing and are skipped.
 // One MMA per K step covers all five ACT panels (N = 160: h1 hi | aug | h1 lo), so the stacked
 // dz2 operand is fetched from shared memory once.
@@ -417,6 +420,7 @@ struct Cta {
     // h1 = tanh(W1 x + b1) of the rows published in sX, into registers: thread (w, l) owns features
     // f0..f0+3 of rows 16*rbk + rs + 4i (i < 4); store_h1() later writes them as tf32 hi/lo panels
     // (a quarter-warp writes the 8 chunks of one row: conflict-free)
+    template <int I0 = 0, int I1 = 4>
     __device__ __forceinline__ void layer1(float (&hreg)[4][4]) const {
         const int pn = w & 1, rbk = w >> 1, j = l & 7, rs = l >> 3, f0 = 32 * pn + 4 * j;
         float w1[4][O], bb[4];
@@ -427,7 +431,7 @@ struct Cta {
             for (int o = 0; o < O; ++o) w1[q][o] = sW1[(f0 + q) * O + o];
         }
 #pragma unroll
-        for (int i = 0; i < 4; ++i) {
+        for (int i = I0; i < I1; ++i) {
             const int r = 16 * rbk + rs + 4 * i;
             const float4 xv = *reinterpret_cast<const float4*>(sX + r * 4);
             const float x[4] = {xv.x, xv.y, xv.z, xv.w};
@@ -488,10 +492,12 @@ struct Cta {
             const int valid = (int)((a.mb - m0) < R ? (a.mb - m0) : R);
             const int nks = (valid + 7) >> 3;
             const bool has_next = tile + stride < ntiles;
+            // ---- h1 panels from registers; aug panel row = [1 x_hi 0.. | 0 x_lo 0..]
+            // The previous tile's GEMM3 (the last reader of the h1 panels) was waited for in its EPI2; only
+            // its GEMM4 may still run, and that reads the DZ and aug panels: the h1 stores go first.
+            store_h1(hreg);
             if (tiles_done > 0) mbar_wait(bar4, par ^ 1);  // every MMA of the previous tile has drained
             stamp(2 + 10 * it);
-            // ---- h1 panels from registers; aug panel row = [1 x_hi 0.. | 0 x_lo 0..]
-            store_h1(hreg);
             if (tid < R) {
                 const float4 xv = *reinterpret_cast<const float4*>(sX + tid * 4);
                 const float xs[4] = {xv.x, xv.y, xv.z, xv.w};

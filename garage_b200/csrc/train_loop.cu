@@ -121,10 +121,14 @@ __device__ __forceinline__ float slice_allreduce(const NetLoop& n, bool own, int
 // Barrier over the CTAs of one network (all co-resident): arrive = one release-reduction (no reply
 // to wait for), wait = acquire loads until the count reaches `target`.  bar.sync orders the other
 // threads' writes before thread 0's release and thread 0's acquire before their later reads.
-__device__ __forceinline__ void net_barrier(unsigned int* ctr, unsigned int target) {
+// The two halves are separate calls so that work which does not depend on the other CTAs (the rows
+// of the next minibatch) runs between "my partial row is published" and "everybody's is".
+__device__ __forceinline__ void net_barrier_arrive(unsigned int* ctr) {
     __syncthreads();
+    if (threadIdx.x == 0) asm volatile("red.release.gpu.global.add.u32 [%0], 1;" ::"l"(ctr) : "memory");
+}
+__device__ __forceinline__ void net_barrier_wait(unsigned int* ctr, unsigned int target) {
     if (threadIdx.x == 0) {
-        asm volatile("red.release.gpu.global.add.u32 [%0], 1;" ::"l"(ctr) : "memory");
         unsigned int v;
         unsigned int spin = 0;
         do {
@@ -133,6 +137,10 @@ __device__ __forceinline__ void net_barrier(unsigned int* ctr, unsigned int targ
         } while (v < target);
     }
     __syncthreads();
+}
+__device__ __forceinline__ void net_barrier(unsigned int* ctr, unsigned int target) {
+    net_barrier_arrive(ctr);
+    net_barrier_wait(ctr, target);
 }
 
 template <int O, int A>
@@ -205,8 +213,14 @@ __device__ __forceinline__ void net_loop(const NetLoop& n, int j, int ctas, uint
         }
         LOOP_STAMP(1);
         const float inv_mb = 1.0f / ((float)a.mb * (float)(n.world > 1 ? n.world : 1));  // the minibatch spans all ranks
-        if (gstep + 1 < total) {  // rows of the next minibatch: independent of the update, start them now
-            set_next_step(a);
+        if (live) {  // publish this CTA's partial row first: the others wait for it, not for what follows
+            cta.write_partial(out, false);
+            cta.stamps = nullptr;
+            LOOP_STAMP(2);
+            net_barrier_arrive(n.sync);
+        }
+        if (gstep + 1 < total) {  // rows of the next minibatch: independent of the update, gathered while the
+            set_next_step(a);     // other CTAs finish their tiles
             LOOP_STAMP(8);
             cta.prime(a, j, ctas);
         }
@@ -219,10 +233,7 @@ __device__ __forceinline__ void net_loop(const NetLoop& n, int j, int ctas, uint
             vv = n.adam_v[pidx];
             pp = __ldcg(n.params + pidx);
         }
-        cta.write_partial(out, false);
-        cta.stamps = nullptr;
-        LOOP_STAMP(2);
-        net_barrier(n.sync, ++nbar * (unsigned int)ctas);
+        net_barrier_wait(n.sync, ++nbar * (unsigned int)ctas);
         LOOP_STAMP(3);
         // ---- fixed-order reduction of this CTA's parameter slice + Adam (reduce_adam_kernel's arithmetic)
         {

@@ -83,11 +83,11 @@ def main():
                     print('tile{} {:36s} {:8.0f} {:8.0f}'.format(it, stage[q], np.median(tt[:, i] - prev), np.median(tt[:, i] - tt[:, 0])))
                     prev = tt[:, i]
         for k in range(len(nets)):
-            print('--- net', k, 'after tiles: set_step {:.0f}, prime {:.0f}, rest until partial written {:.0f}'.format(
-                np.median(t[k][:, 8] - t[k][:, 1]), np.median(t[k][:, 9] - t[k][:, 8]), np.median(t[k][:, 2] - t[k][:, 9])))
+            print('--- net', k, 'between barrier-1 arrive and wait: set_step {:.0f}, prime {:.0f}, remaining wait {:.0f}'.format(
+                np.median(t[k][:, 8] - t[k][:, 2]), np.median(t[k][:, 9] - t[k][:, 8]), np.median(t[k][:, 3] - t[k][:, 9])))
         for k in range(len(nets)):
-            print('--- net', k, 'stamp 9 -> write_partial entry {:.0f}, write_partial exit -> stamp 2 {:.0f}'.format(
-                np.median(tiles[k][:, 28] - t[k][:, 9]), np.median(t[k][:, 2] - tiles[k][:, 30])))
+            print('--- net', k, 'tiles done -> write_partial entry {:.0f}, write_partial exit -> stamp 2 {:.0f}'.format(
+                np.median(tiles[k][:, 28] - t[k][:, 1]), np.median(t[k][:, 2] - tiles[k][:, 30])))
         for k in range(len(nets)):
             tt = tiles[k]
             print('--- net', k, 'write_partial: drain wait {:.0f}, TMEM->smem->global {:.0f} (median cycles)'.format(
