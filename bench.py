@@ -467,17 +467,21 @@ def dist_parity(rank, world, device):
     import torch
     import torch.distributed as dist
 
-    def run(mode):
+    def run(mode, use_peer=None):
         algo, policy, vf, sampler = _pendulum_algo(64, 40, 1024, 3, rank, mode)
+        algo._use_peer = use_peer  # None: default (peer memory); False: NCCL for the small exchanges
         for it in range(2):
             eps = sampler.obtain_samples(it, 64 * 40, policy)
             algo._train_once(it, eps)
         torch.cuda.synchronize()
-        return policy.flat.clone(), vf.flat.clone(), algo._comm is not None
+        return policy.flat.clone(), vf.flat.clone(), algo._comm is not None, dict(algo.last_stats)
 
     rel = lambda x, y: float((x.double() - y.double()).norm() / y.double().norm())
-    pf, vf_, used_peer = run('fused')
-    ps, vs, _ = run('stepwise')
+    pf, vf_, used_peer, logs_peer = run('fused')
+    ps, vs, _, logs_nccl = run('stepwise', use_peer=False)
+    # advantage moments + logging scalars: peer-memory exchange kernel vs NCCL + host arithmetic
+    log_err = max(abs(float(logs_peer[k]) - float(logs_nccl[k])) / max(1.0, abs(float(logs_nccl[k])))
+                  for k in logs_nccl if k in logs_peer and logs_nccl[k] == logs_nccl[k])
     errs = torch.tensor([rel(pf, ps), rel(vf_, vs)], device=device)
     ref = pf.clone()
     dist.broadcast(ref, 0)
@@ -487,6 +491,7 @@ def dist_parity(rank, world, device):
     return dict(fused_vs_nccl_stepwise_rel_err=float(errs.max()), policy_rel_err=float(errs[0]),
                 vf_rel_err=float(errs[1]), ranks_bit_identical=bool(same.item()),
                 fused_used_peer_memory=bool(used_peer), world=world,
+                logs_peer_vs_nccl_max_rel_err=log_err, logged_keys_compared=len(logs_nccl),
                 workload='PPO Pendulum 64 envs x 40 steps per rank, 2 iterations, E=3, global minibatch 1,024')
 
 

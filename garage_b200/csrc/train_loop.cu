@@ -52,9 +52,12 @@ constexpr int COMM_P = 4608;  // per-network capacity of the exchange area (para
 // independent accesses in unspecified order; a scalar b64 access is single-copy atomic), so the
 // sequence number doubles as the "data ready" flag and no system-scope fence (a multi-microsecond
 // drain of every outstanding NVLink write) is needed.
-__device__ __forceinline__ void st_slot(unsigned long long* p, float v, unsigned int seq) {
-    const unsigned long long word = ((unsigned long long)seq << 32) | (unsigned long long)__float_as_uint(v);
+__device__ __forceinline__ void st_slot_bits(unsigned long long* p, unsigned int bits, unsigned int seq) {
+    const unsigned long long word = ((unsigned long long)seq << 32) | (unsigned long long)bits;
     asm volatile("st.relaxed.sys.global.b64 [%0], %1;" ::"l"(p), "l"(word) : "memory");
+}
+__device__ __forceinline__ void st_slot(unsigned long long* p, float v, unsigned int seq) {
+    st_slot_bits(p, __float_as_uint(v), seq);
 }
 __device__ __forceinline__ unsigned long long ld_slot(const unsigned long long* p) {
     unsigned long long word;
@@ -389,9 +392,127 @@ static int launch_loop(const LoopArgs& args, int grid, cudaStream_t s) {
 }
 
 constexpr size_t recv_bytes_c = (size_t)B2G_MAX_RANKS * 2 * COMM_P * 8;
+constexpr int SMALL_N = 64;                                   // doubles per rank of b2g_peer_reduce_f64
+constexpr size_t small_off_c = 2 * recv_bytes_c + 256;        // [src rank][parity][2 * SMALL_N] slots of 8 bytes
+constexpr size_t small_bytes_c = (size_t)B2G_MAX_RANKS * 2 * (2 * SMALL_N) * 8;
 extern "C" int64_t b2g_train_comm_bytes(void) {
-    // per network: receive area [ranks][2][COMM_P] slots of 8 bytes; then the two step counters of this rank
-    return (int64_t)(2 * recv_bytes_c + 256);
+    // per network: receive area [ranks][2][COMM_P] slots of 8 bytes; then 256 bytes of sequence counters
+    // of this rank (two networks, small exchange); then the receive area of b2g_peer_reduce_f64
+    return (int64_t)(small_off_c + small_bytes_c);
+}
+
+// ---- small all-gather + combine over the same peer-mapped buffers (advantage moments, logging scalars) ----
+// One block per rank.  Thread i < 2n owns one 32-bit half of the rank's n doubles: it stores
+// {half, seq} into every peer's receive area, polls its own area for the same half of every other
+// rank (all polls in flight together) and leaves the gathered values in shared memory in rank order;
+// thread 0 then combines them -- in rank order, so every rank computes identical bits.
+struct PeerSmall {
+    unsigned long long* recv[B2G_MAX_RANKS];
+    unsigned int* seq_ptr;
+    int world, rank, n, op;
+    const double* in;
+    double* out;
+    double scalar0, scalar1;  // op 1: local element count; op 2: local sample count B, local episode count
+};
+__global__ void __launch_bounds__(2 * SMALL_N) peer_small_kernel(const PeerSmall q) {
+    __shared__ double send[SMALL_N];
+    __shared__ __align__(8) unsigned int halves[B2G_MAX_RANKS][2 * SMALL_N];
+    const int i = threadIdx.x;
+    if (i == 0) {
+        if (q.op == B2G_PEER_MOMENTS) {  // [count, mean, sum of squared deviations, min]
+            send[0] = q.scalar0; send[1] = q.in[0]; send[2] = q.in[1] * (q.scalar0 - 1.0); send[3] = q.in[2];
+        } else if (q.op == B2G_PEER_LOGS) {
+            const double ne = q.scalar1, mean = q.in[33], sd = q.in[34];
+            for (int k = 0; k < 32; ++k) send[k] = q.in[k];
+            send[32] = ne; send[33] = ne * q.in[32]; send[34] = ne * mean; send[35] = ne * (sd * sd + mean * mean);
+            send[36] = ne * q.in[37]; send[37] = ne * q.in[38]; send[38] = q.in[39]; send[39] = q.scalar0;
+            send[40] = q.in[35]; send[41] = -q.in[36];
+        } else {
+            for (int k = 0; k < q.n; ++k) send[k] = q.in[k];
+        }
+    }
+    __syncthreads();
+    const unsigned int seq = *reinterpret_cast<volatile unsigned int*>(q.seq_ptr) + 1u;
+    const int par = (int)(seq & 1u);
+    if (i < 2 * q.n) {
+        const unsigned int mine = reinterpret_cast<const unsigned int*>(send)[i];
+        halves[q.rank][i] = mine;
+        for (int r = 0; r < q.world; ++r)
+            if (r != q.rank) st_slot_bits(q.recv[r] + ((size_t)(q.rank * 2 + par) * (2 * SMALL_N) + i), mine, seq);
+        unsigned int missing = 0;
+        for (int r = 0; r < q.world; ++r)
+            if (r != q.rank) missing |= 1u << r;
+        const unsigned long long* base = q.recv[q.rank] + ((size_t)par * (2 * SMALL_N) + i);
+        unsigned long long t0 = 0;
+        for (unsigned int spin = 0; missing; ++spin) {
+            unsigned long long wd[B2G_MAX_RANKS];
+#pragma unroll
+            for (int r = 0; r < B2G_MAX_RANKS; ++r)
+                wd[r] = (missing & (1u << r)) ? ld_slot(base + (size_t)r * 2 * (2 * SMALL_N)) : 0ull;
+#pragma unroll
+            for (int r = 0; r < B2G_MAX_RANKS; ++r)
+                if ((missing & (1u << r)) && (unsigned int)(wd[r] >> 32) == seq) {
+                    halves[r][i] = (unsigned int)wd[r];
+                    missing &= ~(1u << r);
+                }
+            if ((spin & 0xfffu) == 0xfffu) {
+                const unsigned long long now = global_ns();
+                if (t0 == 0) t0 = now;
+                else if (now - t0 > g_peer_timeout_ns) __trap();
+            }
+        }
+    }
+    __syncthreads();
+    if (i == 0) {
+        *q.seq_ptr = seq;
+        auto val = [&](int r, int k) { return reinterpret_cast<const double*>(halves[r])[k]; };
+        if (q.op == B2G_PEER_MOMENTS) {
+            // Chan et al.: mean and sum of squared deviations of the union from per-rank (n, mean, M2)
+            double ntot = 0.0, wsum = 0.0, mn = val(0, 3);
+            for (int r = 0; r < q.world; ++r) { ntot += val(r, 0); wsum += val(r, 0) * val(r, 1); mn = fmin(mn, val(r, 3)); }
+            const double mean = wsum / ntot;
+            double m2 = 0.0;
+            for (int r = 0; r < q.world; ++r) { const double d = val(r, 1) - mean; m2 += val(r, 2) + val(r, 0) * d * d; }
+            q.out[0] = mean; q.out[1] = m2 / (ntot - 1.0); q.out[2] = mn;
+        } else if (q.op == B2G_PEER_LOGS) {
+            double t[40], mx = val(0, 40), mnn = val(0, 41);
+            for (int k = 0; k < 40; ++k) {
+                double a = 0.0;
+                for (int r = 0; r < q.world; ++r) a += val(r, k);
+                t[k] = a;
+            }
+            for (int r = 1; r < q.world; ++r) { mx = fmax(mx, val(r, 40)); mnn = fmax(mnn, val(r, 41)); }
+            const double nt = t[32], gmean = t[34] / nt;
+            for (int k = 0; k < 32; ++k) q.out[k] = t[k];
+            q.out[32] = t[33] / nt; q.out[33] = gmean; q.out[34] = sqrt(fmax(t[35] / nt - gmean * gmean, 0.0));
+            q.out[35] = mx; q.out[36] = -mnn; q.out[37] = t[36] / nt; q.out[38] = t[37] / nt; q.out[39] = t[38];
+            q.out[48] = t[39]; q.out[49] = nt; q.out[50] = 1.0;  // [40:48] (this rank's pad-KL statistics) stay
+        } else {
+            for (int r = 0; r < q.world; ++r)
+                for (int k = 0; k < q.n; ++k) q.out[r * q.n + k] = val(r, k);
+        }
+    }
+}
+
+extern "C" int b2g_peer_reduce_f64(const b2g_train_comm* comm, int op, const double* in, int n, double scalar0,
+                                   double scalar1, double* out, void* stream) {
+    B2G_CHECK_ARG(comm && comm->world >= 1 && comm->world <= B2G_MAX_RANKS && comm->rank >= 0 && comm->rank < comm->world,
+                  "bad world/rank");
+    B2G_CHECK_ARG(in && out, "NULL pointer");
+    B2G_CHECK_ARG(op >= B2G_PEER_GATHER && op <= B2G_PEER_LOGS, "bad op");
+    PeerSmall q{};
+    q.n = op == B2G_PEER_MOMENTS ? 4 : (op == B2G_PEER_LOGS ? 42 : n);
+    B2G_CHECK_ARG(q.n > 0 && q.n <= SMALL_N, "1..64 doubles per rank");
+    q.world = comm->world; q.rank = comm->rank; q.op = op; q.in = in; q.out = out;
+    q.scalar0 = scalar0; q.scalar1 = scalar1;
+    for (int r = 0; r < comm->world; ++r) {
+        B2G_CHECK_ARG(comm->peer_base[r] != nullptr, "NULL peer buffer");
+        q.recv[r] = reinterpret_cast<unsigned long long*>(reinterpret_cast<uint8_t*>(comm->peer_base[r]) + small_off_c);
+    }
+    q.seq_ptr = reinterpret_cast<unsigned int*>(reinterpret_cast<uint8_t*>(comm->peer_base[comm->rank]) + 2 * recv_bytes_c) + 32;
+    peer_small_kernel<<<1, 2 * SMALL_N, 0, (cudaStream_t)stream>>>(q);
+    B2G_CHECK_LAUNCH();
+    return B2G_OK;
 }
 
 extern "C" int b2g_mlp_train_loop(const b2g_train_net* nets, int n_nets, float* workspace,

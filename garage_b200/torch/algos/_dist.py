@@ -108,6 +108,24 @@ class PeerComm:
     def struct(self):
         return self._c
 
+    PEER_GATHER, PEER_MOMENTS, PEER_LOGS = 0, 1, 2
+
+    def reduce_f64(self, op, t_in, out, scalar0=0.0, scalar1=0.0, n=0):
+        """b2g_peer_reduce_f64: small all-gather + combine of float64 scalars over the peer-mapped
+        buffers (no NCCL, no host synchronisation, CUDA-graph capturable).  Collective: every rank
+        calls it in the same order."""
+        import ctypes
+
+        from garage_b200 import _lib
+        if t_in.dtype != torch.float64 or out.dtype != torch.float64 or not t_in.is_cuda or not out.is_cuda:
+            raise TypeError('reduce_f64 needs float64 CUDA tensors')
+        if not (t_in.is_contiguous() and out.is_contiguous()):
+            raise ValueError('reduce_f64 needs contiguous tensors')
+        with torch.cuda.device(t_in.device):
+            _lib.call('b2g_peer_reduce_f64', ctypes.byref(self._c), int(op), t_in.data_ptr(), int(n), float(scalar0),
+                      float(scalar1), out.data_ptr(), torch.cuda.current_stream(t_in.device).cuda_stream)
+        return out
+
     def close(self):
         from garage_b200 import _lib
         for p in self._peers:

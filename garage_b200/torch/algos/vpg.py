@@ -97,6 +97,7 @@ class VPG(RLAlgorithm):
             raise ValueError("update_mode must be 'auto', 'fused' or 'stepwise'")
         self._update_mode = update_mode
         self._comm = None
+        self._use_peer = None
         self._dist_B = None
         self.last_stats = {}
 
@@ -125,6 +126,7 @@ class VPG(RLAlgorithm):
         re-created on first use after `Trainer.restore`."""
         state = self.__dict__.copy()
         state['_comm'] = None
+        state['_use_peer'] = None
         state['_pg'] = None
         state['_dist_B'] = None
         return state
@@ -132,6 +134,17 @@ class VPG(RLAlgorithm):
     # ------------------------------------------------------------ distributed --
     def _world(self):
         return _dist.world_size(self._pg)
+
+    def _peer_comm(self):
+        """The peer-mapped exchange buffers of this job (one node, CUDA IPC), created on first use by
+        a COLLECTIVE call -- every rank reaches its first use at the same point of the same
+        iteration.  None when B2G_PEER_STATS=0 asks for the NCCL path of the small exchanges."""
+        if self._comm is None and self._use_peer is None:
+            import os
+            self._use_peer = os.environ.get('B2G_PEER_STATS', '1') != '0'
+        if self._comm is None and self._use_peer:
+            self._comm = _dist.PeerComm(self.policy.flat.device, self._pg)
+        return self._comm if self._use_peer else None
 
     # ---------------------------------------------------------------- prepare --
     def _entropy_value(self, log_std):
@@ -272,7 +285,11 @@ class VPG(RLAlgorithm):
             return adv
         stats = ops.moments(adv)
         if self._world() > 1:
-            stats = _dist.combine_moments(stats, adv.numel(), self._pg)
+            comm = self._peer_comm()
+            if comm is not None:  # 4 doubles per rank through peer memory, combined in one small kernel
+                stats = comm.reduce_f64(comm.PEER_MOMENTS, stats, torch.empty_like(stats), scalar0=adv.numel())
+            else:
+                stats = _dist.combine_moments(stats, adv.numel(), self._pg)
         return ops.normalize_adv(adv, stats, self._center_adv, self._positive_adv)
 
     # ------------------------------------------------------------ loss set-up --
@@ -450,6 +467,7 @@ class VPG(RLAlgorithm):
                 else:
                     if self._comm is None:
                         self._comm = _dist.PeerComm(f.obs.device, self._pg)
+                        self._use_peer = self._use_peer if self._use_peer is not None else True
                     comm = self._comm
             if world:
                 nets = [self._loop_net(self._policy_optimizer, self.policy, f, True),
@@ -477,7 +495,7 @@ class VPG(RLAlgorithm):
         synchronisation (CUDA-graph capturable when the batch shape is static).
         Returns (stats [48] float64 device tensor, B, n_eps)."""
         f = self._prepare(eps)
-        stats = torch.zeros(48, dtype=torch.float64, device=f.obs.device)
+        stats = torch.zeros(56, dtype=torch.float64, device=f.obs.device)
         pad_kl = self._pad_value_mode == 'reference' and f.fixed_len is None and self._log_stats
         if pad_kl:
             # the reference logs KL over the zero-PADDED observations too (vpg.py:172-173,
@@ -498,6 +516,13 @@ class VPG(RLAlgorithm):
                               **self._policy_kwargs())
             ops.mlp_reduce(self.policy.mlp_shape, nb, 1.0, stats_out=stats[40:48])
             stats[39:40].fill_(float(f.n_eps * int(self.max_episode_length) - f.B))  # padded entries
+        if self._world() > 1:
+            comm = self._peer_comm()
+            if comm is not None:
+                # the logging scalars of all ranks, combined on the device before the single D2H read:
+                # stats[0:40] become the job-wide values, [48] / [49] the job-wide samples / episodes,
+                # [50] marks them as reduced (see _log_iteration)
+                comm.reduce_f64(comm.PEER_LOGS, stats, stats, scalar0=f.B, scalar1=f.n_eps)
         return stats, f.B, f.n_eps
 
     def _train_once(self, itr, eps):
@@ -514,7 +539,10 @@ class VPG(RLAlgorithm):
         B = float(B)
         world = self._world()
         if world > 1:
-            s, B, n_eps = self._reduce_logs(s, B, n_eps, world)
+            if len(s) > 50 and s[50] == 1.0:  # already combined on the device (_enqueue_iteration)
+                B, n_eps = float(s[48]), int(round(s[49]))
+            else:
+                s, B, n_eps = self._reduce_logs(s, B, n_eps, world)
         pol_before, vf_before = s[0] / B, s[8] / B
         pol_after, vf_after = s[16] / B, s[24] / B
         with tabular.prefix(self.policy.name):

@@ -404,6 +404,20 @@ typedef struct b2g_train_comm {
 int64_t b2g_train_comm_bytes(void);
 int b2g_mlp_train_loop_dist(const b2g_train_net* nets, int n_nets, const b2g_train_comm* comm,
                             float* workspace, int64_t workspace_floats, void* stream);
+/* Small all-gather + combine of per-rank float64 scalars through the same peer-mapped buffers (one
+ * block per rank, no NCCL, graph-capturable; every rank calls it in the same order and obtains
+ * identical bits).  Replaces, for several ranks, the host-side arithmetic of
+ *   op B2G_PEER_MOMENTS  vpg.py:371-377: in = b2g_moments' [mean, unbiased var, min] of this
+ *        rank's advantages, scalar0 = their count -> out[3] = the same three over all ranks;
+ *   op B2G_PEER_LOGS     _functions.py:262-273 + vpg.py:186-199: in = the 40 logging statistics of
+ *        this rank (sums [0:32], return statistics [32:39], padded count [39]), scalar0 = samples,
+ *        scalar1 = episodes -> out[0:40]: sums, episode-weighted means, the GLOBAL std, max / min;
+ *        out[48] = samples, out[49] = episodes of all ranks, out[50] = 1 ("reduced"); out[40:48] is
+ *        not written and out may alias in (>= 51 doubles);
+ *   op B2G_PEER_GATHER   out[world][n] = every rank's in[n] (n <= 64). */
+enum { B2G_PEER_GATHER = 0, B2G_PEER_MOMENTS = 1, B2G_PEER_LOGS = 2 };
+int b2g_peer_reduce_f64(const b2g_train_comm* comm, int op, const double* in, int n, double scalar0,
+                        double scalar1, double* out, void* stream);
 int b2g_comm_alloc(int64_t bytes, void** ptr_out, void* handle_out_64);
 int b2g_comm_open(const void* handle_64, void** ptr_out);
 int b2g_comm_close(void* ptr);
