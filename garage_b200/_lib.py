@@ -103,6 +103,12 @@ SIGNATURES = {
     'b2g_mlp_train_loop': (c_int, [POINTER(TrainNet), c_int, P, c_int64, P]),
     'b2g_train_comm_bytes': (c_int64, []),
     'b2g_mlp_train_loop_dist': (c_int, [POINTER(TrainNet), c_int, POINTER(TrainComm), P, c_int64, P]),
+    'b2g_mlp_fvp': (c_int, [c_int, c_int, c_int, P, P, P, c_int64, c_int64, P, c_float, c_float, c_float, P, P, P, P]),
+    'b2g_cg_init': (c_int, [P, P, P, P, P, c_int, P]),
+    'b2g_cg_step': (c_int, [P, P, P, P, P, c_int, c_double, P]),
+    'b2g_cg_sanitize': (c_int, [P, c_int, P]),
+    'b2g_cg_descent': (c_int, [P, P, c_double, P, P, c_int, P]),
+    'b2g_line_search_point': (c_int, [P, P, c_float, P, c_int, P]),
     'b2g_peer_reduce_f64': (c_int, [POINTER(TrainComm), c_int, P, c_int, c_double, c_double, P, P]),
     'b2g_comm_alloc': (c_int, [c_int64, POINTER(c_void_p), ctypes.c_char_p]),
     'b2g_comm_open': (c_int, [ctypes.c_char_p, POINTER(c_void_p)]),

@@ -1,6 +1,7 @@
 // Host launchers for the fused MLP minibatch kernel, partial-gradient reduction,
 // Adam, and the forward-only evaluation paths.
 #include "mlp_tc.cuh"
+#include "mlp_general.cuh"
 #include <stdlib.h>
 
 // CTAs per launch: one per 128-row tile, capped at SMs x resident CTAs per SM
@@ -38,16 +39,16 @@ static int launch_mlp(const MlpArgs& a, cudaStream_t s) {
 }
 
 // ---- tensor-core path (hidden 64): one CTA per SM, 128-row tiles
-static int g_mlp_path = -1;  // 0 auto (tcgen05 for hidden 64 backward), 1 CUDA-core fp32 only, 2 = 0
+static int g_mlp_path = -1;  // 0 auto (tcgen05 for hidden 64 backward), 1 CUDA-core fp32 only, 2 = 0, 3 general-shape kernels
 static int mlp_path() {
     if (g_mlp_path < 0) {
         const char* e = getenv("B2G_MLP_PATH");
-        g_mlp_path = (e && (e[0] == 'f' || e[0] == '1')) ? 1 : 0;   // "ffma" / "1" forces the CUDA-core kernel
+        g_mlp_path = (e && (e[0] == 'f' || e[0] == '1')) ? 1 : ((e && (e[0] == 'g' || e[0] == '3')) ? 3 : 0);
     }
     return g_mlp_path;
 }
 extern "C" int b2g_set_mlp_path(int path) {
-    B2G_CHECK_ARG(path >= 0 && path <= 2, "path must be 0 (auto), 1 (CUDA-core fp32) or 2 (tcgen05)");
+    B2G_CHECK_ARG(path >= 0 && path <= 3, "path must be 0 (auto), 1 (CUDA-core fp32), 2 (tcgen05) or 3 (general-shape kernels)");
     g_mlp_path = path == 2 ? 0 : path;
     return B2G_OK;
 }
@@ -57,8 +58,7 @@ extern "C" int b2g_get_mlp_path(void) { return mlp_path(); }
 static long long* g_mlp_timing = nullptr;
 extern "C" int b2g_mlp_debug_timing(long long* buf) { g_mlp_timing = buf; return B2G_OK; }
 
-template <int H, int O, int A>
-constexpr bool mlp_has_tc() { return H == 64; }
+static bool force_general() { return mlp_path() == 3; }
 
 static int mlp_tc_grid(int64_t rows) {
     const int64_t tiles = (rows + tc::R - 1) / tc::R;
@@ -102,12 +102,39 @@ static int launch_mlp_eval_tc(const MlpArgs& a, cudaStream_t s) {
 
 static int mlp_unsupported(int O, int H, int A) {
     b2g_set_error("MLP shape obs=%d hidden=(%d,%d) out=%d is not built into libb2g "
-                  "(built: obs in {3,4}, hidden in {32,64}, out in {1,2})", O, H, H, A);
+                  "(built: obs 1..8, hidden in {32,64,128}, out 1..4)", O, H, H, A);
     return B2G_ERR_UNSUPPORTED;
 }
 
+// ---- general shapes (mlp_general.cuh): capacities the kernels are compiled for
+int b2g_gen_launch_h32(int mode, int op, int ap, const MlpArgs& a, cudaStream_t s);
+int b2g_gen_launch_h64(int mode, int op, int ap, const MlpArgs& a, cudaStream_t s);
+int b2g_gen_launch_h128(int mode, int op, int ap, const MlpArgs& a, cudaStream_t s);
+int b2g_gen_grid_h32(int mode, int op, int ap, int64_t rows);
+int b2g_gen_grid_h64(int mode, int op, int ap, int64_t rows);
+int b2g_gen_grid_h128(int mode, int op, int ap, int64_t rows);
+static bool gen_supported(int O, int H, int A) {
+    return (H == 32 || H == 64 || H == 128) && O >= 1 && O <= 8 && A >= 1 && A <= 4;
+}
+static int gen_op(int O) { return O <= 4 ? 4 : 8; }
+static int gen_ap(int A) { return A <= 1 ? 1 : (A == 2 ? 2 : 4); }
+static int gen_launch(int mode, int O, int H, int A, MlpArgs a, cudaStream_t s) {
+    a.O_rt = O; a.A_rt = A;
+    if (H == 32) return b2g_gen_launch_h32(mode, gen_op(O), gen_ap(A), a, s);
+    if (H == 64) return b2g_gen_launch_h64(mode, gen_op(O), gen_ap(A), a, s);
+    return b2g_gen_launch_h128(mode, gen_op(O), gen_ap(A), a, s);
+}
+static int gen_grid(int mode, int O, int H, int A, int64_t rows) {
+    if (H == 32) return b2g_gen_grid_h32(mode, gen_op(O), gen_ap(A), rows);
+    if (H == 64) return b2g_gen_grid_h64(mode, gen_op(O), gen_ap(A), rows);
+    return b2g_gen_grid_h128(mode, gen_op(O), gen_ap(A), rows);
+}
+// path 3 (B2G_MLP_PATH=general / b2g_set_mlp_path(3)): every shape through the general kernels (tests)
+static bool force_general();
+
 template <bool BWD>
 static int dispatch_mlp(int O, int H, int A, const MlpArgs& a, cudaStream_t s) {
+    if (force_general() && gen_supported(O, H, A)) return gen_launch(BWD ? 1 : 0, O, H, A, a, s);
 #define B2G_CASE(HH, OO, AA)                                                         \
     if (H == HH && O == OO && A == AA) {                                             \
         if constexpr (HH == 64) {                                                    \
@@ -117,12 +144,15 @@ static int dispatch_mlp(int O, int H, int A, const MlpArgs& a, cudaStream_t s) {
     }
     B2G_MLP_SHAPES(B2G_CASE)
 #undef B2G_CASE
+    if (gen_supported(O, H, A)) return gen_launch(BWD ? 1 : 0, O, H, A, a, s);
     return mlp_unsupported(O, H, A);
 }
 
 // number of per-CTA partial rows a launch over `rows` rows writes (<0: unsupported shape)
 extern "C" int b2g_mlp_num_partials(int obs_dim, int hidden, int out_dim, int backward,
                                     int64_t rows) {
+    if (force_general() && gen_supported(obs_dim, hidden, out_dim))
+        return gen_grid(backward ? 1 : 0, obs_dim, hidden, out_dim, rows);
 #define B2G_CASE(HH, OO, AA)                                                                   \
     if (hidden == HH && obs_dim == OO && out_dim == AA) {                                      \
         if (HH == 64 && mlp_path() == 0) return mlp_tc_grid(rows);                             \
@@ -130,6 +160,7 @@ extern "C" int b2g_mlp_num_partials(int obs_dim, int hidden, int out_dim, int ba
     }
     B2G_MLP_SHAPES(B2G_CASE)
 #undef B2G_CASE
+    if (gen_supported(obs_dim, hidden, out_dim)) return gen_grid(backward ? 1 : 0, obs_dim, hidden, out_dim, rows);
     return mlp_unsupported(obs_dim, hidden, out_dim);
 }
 
@@ -280,6 +311,54 @@ extern "C" int b2g_adam_step(float* params, const float* grad, float grad_scale,
     B2G_CHECK_ARG(params && grad && adam_m && adam_v && step_counter && n > 0, "bad arguments");
     adam_kernel<<<(n + 255) / 256, 256, 0, (cudaStream_t)stream>>>(params, grad, grad_scale, adam_m, adam_v,
                                                                    step_counter, lr, beta1, beta2, eps, n);
+    B2G_CHECK_LAUNCH();
+    return B2G_OK;
+}
+
+// ------------------------------------------------ Fisher-vector product --
+// out = (1/n) sum_rows J_r^T diag(1/var) J_r vec  (+ 2 A vec[log_std] on the log_std entry when the
+// clamp passes) + reg_coeff * vec: the Hessian of mean KL(old || new) at new == old for the
+// state-independent-std Gaussian head, i.e. what `_build_hessian_vector_product(f_constraint, ...)`
+// (torch/optimizers/conjugate_gradient_optimizer.py:18-66) returns with `f_constraint` =
+// `VPG._compute_kl_constraint` (torch/algos/vpg.py:381-406) when the step starts at the old policy
+// (TRPO's default full-batch single-epoch update, trpo.py:119-144).  The second-order term of the
+// network vanishes there because it multiplies (mu_old - mu_new) = 0, so the Gauss-Newton product is exact.
+__global__ void fvp_finish_kernel(float* __restrict__ out, const float* __restrict__ vec,
+                                  const float* __restrict__ params, int P, int A, float min_ls, float max_ls,
+                                  float reg) {
+    const int p = blockIdx.x * blockDim.x + threadIdx.x;
+    if (p >= P) return;
+    float v = out[p] + reg * vec[p];
+    if (p == 0) {
+        const float raw = params[0];
+        out[0] = reg * vec[0] + ((raw >= min_ls && raw <= max_ls) ? 2.0f * (float)A * vec[0] : 0.0f);
+        return;
+    }
+    out[p] = v;
+}
+
+extern "C" int b2g_mlp_fvp(int obs_dim, int hidden, int out_dim, const float* params, const float* vec,
+                           const int32_t* idx, int64_t start, int64_t n, const float* obs,
+                           float min_log_std, float max_log_std, float reg_coeff, float* u_scratch,
+                           float* ws_partial, float* out, void* stream) {
+    B2G_CHECK_ARG(n > 0, "empty batch");
+    B2G_CHECK_ARG(params && vec && obs && u_scratch && ws_partial && out, "NULL pointer");
+    if (!gen_supported(obs_dim, hidden, out_dim)) return mlp_unsupported(obs_dim, hidden, out_dim);
+    cudaStream_t s = (cudaStream_t)stream;
+    MlpArgs a{};
+    a.params = params; a.idx = idx; a.start = start; a.mb = n; a.obs = obs;
+    a.loss_kind = LOSS_NONE; a.min_log_std = min_log_std; a.max_log_std = max_log_std;
+    a.partial = ws_partial; a.vparams = vec; a.mean_out = u_scratch;
+    int rc = gen_launch(gen::M_JVP, obs_dim, hidden, out_dim, a, s);
+    if (rc != B2G_OK) return rc;
+    a.vparams = nullptr; a.mean_out = nullptr; a.dmu_in = u_scratch; a.loss_kind = LOSS_GIVEN;
+    rc = gen_launch(gen::M_BWD, obs_dim, hidden, out_dim, a, s);
+    if (rc != B2G_OK) return rc;
+    const int P = MlpLayout{obs_dim, hidden, out_dim}.total();
+    rc = b2g_mlp_reduce(ws_partial, gen_grid(gen::M_BWD, obs_dim, hidden, out_dim, n), P, 1.0f / (float)n, out, nullptr,
+                        nullptr, nullptr, nullptr, nullptr, 0.0, 0.0, 0.0, 0.0, stream);
+    if (rc != B2G_OK) return rc;
+    fvp_finish_kernel<<<(P + 255) / 256, 256, 0, s>>>(out, vec, params, P, out_dim, min_log_std, max_log_std, reg_coeff);
     B2G_CHECK_LAUNCH();
     return B2G_OK;
 }

@@ -18,7 +18,8 @@
 #pragma once
 #include "mlp.cuh"
 
-enum : int { LOSS_PPO = 0, LOSS_VPG = 1, LOSS_VF = 2, LOSS_NONE = 3 };
+enum : int { LOSS_PPO = 0, LOSS_VPG = 1, LOSS_VF = 2, LOSS_NONE = 3,
+              LOSS_GIVEN = 4 };  // d loss / d mean supplied per row (dmu_in): the backward half of a Hessian-vector product
 enum : int {
     FLAG_ENT_REG = 1,        // entropy_method == 'regularized' (vpg.py:341-343)
     FLAG_SOFTPLUS_ENT = 2,   // use_softplus_entropy (vpg.py:429-430)
@@ -48,6 +49,10 @@ struct MlpArgs {
     int64_t perm_n;         // 0: off
     int perm_half_bits;
     uint32_t perm_keys[8];
+    // general-shape kernels (mlp_general.cuh): runtime dimensions inside the compiled capacities
+    int O_rt, A_rt;
+    const float* dmu_in;    // [mb,A] LOSS_GIVEN: d loss / d mean per minibatch row
+    const float* vparams;   // tangent vector in the parameter layout (forward-mode pass)
 };
 
 
@@ -79,9 +84,9 @@ __device__ __forceinline__ MlpDist mlp_dist(const MlpArgs& a, float raw_ls) {
 // entropy terms for an action dimension A (sum_a 0.5 + 0.5 log(2 pi) + log(std); F.softplus of it when
 // use_softplus_entropy, vpg.py:429-430)
 template <int A>
-__device__ __forceinline__ void mlp_dist_entropy(const MlpArgs& a, MlpDist& d) {
-    float ent = (float)A * (1.4189385332046727f + d.log_scale);
-    float dent_dls = (float)A;
+__device__ __forceinline__ void mlp_dist_entropy(const MlpArgs& a, MlpDist& d, int A_rt = A) {
+    float ent = (float)A_rt * (1.4189385332046727f + d.log_scale);
+    float dent_dls = (float)A_rt;
     if (a.flags & FLAG_SOFTPLUS_ENT) {
         const float sp = (ent > 20.0f) ? ent : log1pf(expf(ent));
         dent_dls *= (ent > 20.0f) ? 1.0f : 1.0f / (1.0f + expf(-ent));
@@ -122,7 +127,10 @@ __device__ __forceinline__ MlpRowIn<A> mlp_row_in(const MlpArgs& a, int64_t src)
 // FAST uses ex2.approx for the probability ratio (2 ulp; the tensor-core paths).
 template <int A, bool STATS = true, bool FAST = false>
 __device__ __forceinline__ void mlp_row_loss(const MlpArgs& a, const MlpRowIn<A>& in, const float (&mu)[A],
-                                             const MlpDist& ds, float (&dmu)[A], MlpRowAcc& acc) {
+                                             const MlpDist& ds, float (&dmu)[A], MlpRowAcc& acc, int A_rt = A) {
+    // A_rt <= A: action dimensions in use (general-shape kernels compile for a capacity A and keep the
+    // unused means, actions and W3 rows at zero)
+    const float fA = (float)A_rt;
     const float stdv = ds.stdv, log_scale = ds.log_scale, inv_var = ds.inv_var;
     const bool ls_pass = ds.ls_pass;
     const float ent = ds.ent, dent_dls = ds.dent_dls;  // mlp_dist_entropy<A>() ran after mlp_dist()
@@ -130,8 +138,8 @@ __device__ __forceinline__ void mlp_row_loss(const MlpArgs& a, const MlpRowIn<A>
         acc.st_rows += 1.0f;
         acc.st_ent += ent;
     }
-    if (a.loss_kind == LOSS_NONE) {
-        // forward only (baselines / means)
+    if (a.loss_kind == LOSS_NONE || a.loss_kind == LOSS_GIVEN) {
+        // forward only (baselines / means), or d loss / d mean supplied by the caller
     } else if (a.loss_kind == LOSS_VF) {
         // -log N(ret; mu, std): gaussian_mlp_value_function.py:81-97
         const float d = in.ret - mu[0];
@@ -146,7 +154,7 @@ __device__ __forceinline__ void mlp_row_loss(const MlpArgs& a, const MlpRowIn<A>
             dsq += dact[q] * dact[q];
         }
         // Independent(Normal).log_prob: sum_a -(a - mu)^2 / (2 var) - log(std) - log(sqrt(2 pi))
-        ll = -dsq * ds.inv_2var - (float)A * (log_scale + 0.9189385332046727f);
+        ll = -dsq * ds.inv_2var - fA * (log_scale + 0.9189385332046727f);
         const float adv = in.adv;
         float obj, dobj_dll;
         if (a.loss_kind == LOSS_PPO) {  // ppo.py:113-132
@@ -178,14 +186,14 @@ __device__ __forceinline__ void mlp_row_loss(const MlpArgs& a, const MlpRowIn<A>
         const float s = -dobj_dll * inv_var;
 #pragma unroll
         for (int q = 0; q < A; ++q) dmu[q] = s * dact[q];
-        if (ls_pass) acc.gLs -= dobj_dll * (dsq * inv_var - (float)A) + dobj_dls;
+        if (ls_pass) acc.gLs -= dobj_dll * (dsq * inv_var - fA) + dobj_dls;
         if (STATS && a.old_mean) {  // torch kl_normal_normal(old, new), vpg.py:381-406
             const float so = expf(a.old_log_std ? __ldg(a.old_log_std) : 0.0f);
             const float vr = (so / stdv) * (so / stdv);
 #pragma unroll
             for (int q = 0; q < A; ++q) {
                 const float t1 = (in.old_mean[q] - mu[q]) / stdv;
-                acc.st_kl += 0.5f * (vr + t1 * t1 - 1.0f - logf(vr));
+                if (q < A_rt) acc.st_kl += 0.5f * (vr + t1 * t1 - 1.0f - logf(vr));
             }
         }
     }

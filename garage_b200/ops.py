@@ -618,3 +618,59 @@ def gridworld_rollout(gs, max_episode_length, table, buf, t0, n_steps):
              ptr(table), ptr(gs.state), ptr(gs.step_cnt), int(n_steps), gs.n, ptr(buf.obs[t0:]), ptr(buf.act[t0:]),
              ptr(buf.rew[t0:]), ptr(buf.step_type[t0:]), ptr(buf.last_obs[t0:]), ptr(buf.ep_len[t0:]),
              _stream(table))
+
+
+# ------------------------------------------------------------------ TRPO --
+def mlp_fvp(shape, params, vec, obs, *, idx=None, start=0, n=None, min_log_std=-INF, max_log_std=INF,
+            reg_coeff=1e-5, out=None, scratch=None):
+    """Fisher-vector product of the Gaussian MLP policy over `n` rows (b2g_mlp_fvp): the Hessian of
+    mean KL(old || new) at new == old times `vec`, plus reg_coeff * vec."""
+    _chk(params, torch.float32, 'params')
+    _chk(vec, torch.float32, 'vec')
+    _chk(obs, torch.float32, 'obs')
+    _chk(idx, torch.int32, 'idx')
+    if params.numel() != shape.P or vec.numel() != shape.P:
+        raise ValueError('params / vec must have {} elements'.format(shape.P))
+    if n is None:
+        n = idx.numel() if idx is not None else obs.shape[0] - start
+    if out is None:
+        out = torch.empty(shape.P, dtype=torch.float32, device=params.device)
+    if scratch is None or scratch.numel() < n * shape.A:
+        scratch = torch.empty(n * shape.A, dtype=torch.float32, device=params.device)
+    with torch.cuda.device(shape.device):
+        call('b2g_mlp_fvp', shape.O, shape.H, shape.A, ptr(params), ptr(vec), ptr(idx), int(start), int(n),
+             ptr(obs), float(min_log_std), float(max_log_std), float(reg_coeff), ptr(scratch), ptr(shape.ws),
+             ptr(out), _stream(params))
+    return out
+
+
+def cg_init(b, x, r, p, scal):
+    with torch.cuda.device(b.device):
+        call('b2g_cg_init', ptr(b), ptr(x), ptr(r), ptr(p), ptr(scal), int(b.numel()), _stream(b))
+
+
+def cg_step(z, x, r, p, scal, residual_tol=1e-10):
+    with torch.cuda.device(z.device):
+        call('b2g_cg_step', ptr(z), ptr(x), ptr(r), ptr(p), ptr(scal), int(z.numel()), float(residual_tol), _stream(z))
+
+
+def cg_sanitize(x):
+    with torch.cuda.device(x.device):
+        call('b2g_cg_sanitize', ptr(x), int(x.numel()), _stream(x))
+
+
+def cg_descent(x, Ax, max_constraint_value, descent, scal):
+    with torch.cuda.device(x.device):
+        call('b2g_cg_descent', ptr(x), ptr(Ax), float(max_constraint_value), ptr(descent), ptr(scal),
+             int(x.numel()), _stream(x))
+
+
+def line_search_point(prev, descent, ratio, params):
+    with torch.cuda.device(prev.device):
+        call('b2g_line_search_point', ptr(prev), ptr(descent), float(ratio), ptr(params), int(prev.numel()),
+             _stream(prev))
+
+
+def loop_shape_built(shape):
+    """True when the tcgen05 fused training loop is compiled for this (obs, out) pair (hidden 64)."""
+    return shape.H == 64 and (shape.O, shape.A) in ((3, 1), (3, 2), (4, 1))

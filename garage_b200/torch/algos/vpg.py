@@ -406,7 +406,8 @@ class VPG(RLAlgorithm):
         if self._update_mode == 'stepwise':
             return False
         ok = (self.policy.mlp_shape.H == 64 and self._value_function.mlp_shape.H == 64 and
-              ops.mlp_path() == 0)
+              ops.mlp_path() == 0 and self._policy_optimizer.cg is None and self._vf_optimizer.cg is None and
+              ops.loop_shape_built(self.policy.mlp_shape) and ops.loop_shape_built(self._value_function.mlp_shape))
         if not ok and self._update_mode == 'fused':
             raise NotImplementedError("update_mode='fused' needs hidden sizes (64, 64) and the tcgen05 path")
         return ok

@@ -1,10 +1,11 @@
 """OptimizerWrapper drop-in (reference torch/optimizers/optimizer_wrapper.py:6-63 +
 np/optimizers/minibatch_dataset.py:4-35 + make_optimizer _functions.py:25-65).
 
-Same constructor; the optimiser must be `torch.optim.Adam` (the only one on the
-PPO/VPG path: ppo.py:65-76, vpg.py:97-105) -- its state (exp_avg, exp_avg_sq,
-step) lives in flat CUDA vectors next to the module's flat parameter vector and
-the update is libb2g's fused reduce+Adam kernel."""
+Same constructor; the optimiser is `torch.optim.Adam` (the one on the PPO/VPG path:
+ppo.py:65-76, vpg.py:97-105) -- its state (exp_avg, exp_avg_sq, step) lives in flat CUDA
+vectors next to the module's flat parameter vector and the update is libb2g's fused
+reduce+Adam kernel -- or `ConjugateGradientOptimizer` (TRPO's policy optimiser,
+trpo.py:62-66), whose instance is kept in `cg`."""
 import numpy as np
 import torch
 
@@ -18,8 +19,19 @@ class OptimizerWrapper:
             opt_type, opt_args = optimizer
         else:
             opt_type, opt_args = optimizer, {}
+        self._module = module
+        self._max_optimization_epochs = max_optimization_epochs
+        self._minibatch_size = minibatch_size
+        self._state = None
+        self.cg = None
+        from garage_b200.torch.optimizers.conjugate_gradient_optimizer import ConjugateGradientOptimizer
+        if opt_type is ConjugateGradientOptimizer:
+            self.cg = ConjugateGradientOptimizer(None, **opt_args)
+            self.lr = self.beta1 = self.beta2 = self.eps = None
+            return
         if opt_type is not torch.optim.Adam:
-            raise NotImplementedError('garage_b200 implements torch.optim.Adam only (got {})'.format(opt_type))
+            raise NotImplementedError('garage_b200 implements torch.optim.Adam and ConjugateGradientOptimizer '
+                                      '(got {})'.format(opt_type))
         args = dict(_ADAM_DEFAULTS)
         unknown = set(opt_args) - set(args)
         if unknown:
@@ -30,10 +42,6 @@ class OptimizerWrapper:
         self.lr = float(args['lr'])
         self.beta1, self.beta2 = (float(b) for b in args['betas'])
         self.eps = float(args['eps'])
-        self._module = module
-        self._max_optimization_epochs = max_optimization_epochs
-        self._minibatch_size = minibatch_size
-        self._state = None
 
     @property
     def module(self):

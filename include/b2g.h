@@ -468,6 +468,36 @@ int b2g_adam_step(float* params, const float* grad, float grad_scale, float* ada
                   float* adam_v, const unsigned long long* step_counter, double lr, double beta1,
                   double beta2, double eps, int n, void* stream);
 
+/* ---- TRPO: torch/algos/trpo.py:9-144 on torch/optimizers/conjugate_gradient_optimizer.py ----
+ * Fisher-vector product: what `_build_hessian_vector_product(f_constraint, params, reg_coeff)(vec)`
+ * (conjugate_gradient_optimizer.py:18-66) returns for f_constraint = mean KL(old || new)
+ * (torch/algos/vpg.py:381-406) at new == old, where the Hessian of the KL of two diagonal Gaussians with a
+ * state-independent log-std is J^T diag(1/var) J / n on the mean parameters and 2 * out_dim on log_std
+ * (0 when the clamp blocks its gradient):
+ *   out[P] = that matrix times vec[P] + reg_coeff * vec.
+ * One forward-mode pass writes u = (d mu / d theta . vec) / var into u_scratch [n, out_dim], one backward
+ * pass with d loss / d mu := u accumulates J^T u.  Any obs_dim <= 8, out_dim <= 4, hidden in
+ * {32, 64, 128}.  idx/start/n select the rows like b2g_mlp_minibatch_grad; ws_partial as there. */
+int b2g_mlp_fvp(int obs_dim, int hidden, int out_dim, const float* params, const float* vec,
+                const int32_t* idx, int64_t start, int64_t n, const float* obs, float min_log_std,
+                float max_log_std, float reg_coeff, float* u_scratch, float* ws_partial, float* out,
+                void* stream);
+/* `_conjugate_gradient` (conjugate_gradient_optimizer.py:69-110) on float32 vectors of n elements, the
+ * scalars in device memory `scal` (double[8]: [0] r.r, [1] converged flag, [2] step size, [3] x.Ax,
+ * [4] iterations run): init sets x = 0, r = p = b; step consumes z = A p (b2g_mlp_fvp of p) and is a no-op
+ * once r.r < residual_tol -- the reference's `break` without a host synchronisation. */
+int b2g_cg_init(const float* b, float* x, float* r, float* p, double* scal, int n, void* stream);
+int b2g_cg_step(const float* z, float* x, float* r, float* p, double* scal, int n, double residual_tol,
+                void* stream);
+/* `ConjugateGradientOptimizer.step` (:141-178): nan -> 0 in the step direction; then, with Ax = A x,
+ * descent = sqrt(2 max_constraint_value / (x.Ax + 1e-8)) * x (step size 1 if that is nan). */
+int b2g_cg_sanitize(float* x, int n, void* stream);
+int b2g_cg_descent(const float* x, const float* Ax, double max_constraint_value, float* descent,
+                   double* scal, int n, void* stream);
+/* One point of `_backtracking_line_search` (:218-236): params = prev - ratio * descent. */
+int b2g_line_search_point(const float* prev, const float* descent, float ratio, float* params, int n,
+                          void* stream);
+
 /* Random permutation of 0..n-1 as int32 ids (minibatch shuffle; stands in for
  * np.random.shuffle(self._ids), np/optimizers/minibatch_dataset.py:35, in
  * throughput mode -- parity mode passes the reference's own id lists to

@@ -305,6 +305,96 @@ def gen_gridworld():
     np.savez_compressed(os.path.join(OUT, 'gridworld.npz'), **out)
 
 
+def gen_trpo():
+    """reference TRPO (torch/algos/trpo.py) with its default optimisers --
+    ConjugateGradientOptimizer(max_constraint_value=0.01) for the policy, Adam minibatches for the
+    value function -- on a reference LocalSampler batch of PointEnv.  Records the batch, both
+    parameter vectors before / after `_train_once`, the dowel values, and known answers of the
+    optimiser's pieces on the same batch: the loss gradient, Hessian-vector products of the KL
+    constraint (conjugate_gradient_optimizer.py:18-66) for fixed vectors, the CG solution (:69-110)
+    and the accepted step of the line search (:141-260).
+
+    With the default `hvp_reg_coeff=1e-5` the linear system is nearly singular (the Fisher matrix of a
+    few hundred samples has a large null space in which A = 1e-5 I), so 10 CG iterations in float32
+    amplify rounding noise by ~1e5: the reference's own step changes by tens of per cent with the
+    summation order (a float64 replay of the same algorithm lands 0.14 away on a step of 0.13).  The
+    cases `fixed` / `early` therefore pin the well-posed PIECES (gradient, Hessian-vector products,
+    logged values); the cases `*_reg` run the same reference code with
+    `ConjugateGradientOptimizer(hvp_reg_coeff=1.0)`, where CG converges and the whole `_train_once`
+    (line search included) is reproducible to ~1e-5."""
+    import random
+
+    from garage.envs import PointEnv
+    from garage.sampler import LocalSampler
+    from garage.torch.algos import TRPO
+    from garage.torch.optimizers import conjugate_gradient_optimizer as cgo
+    from garage.torch.policies import GaussianMLPPolicy
+    from garage.torch.value_functions import GaussianMLPValueFunction
+    from oracle import ref_shims
+    out = {}
+    from garage.torch.optimizers import ConjugateGradientOptimizer, OptimizerWrapper
+    cases = dict(fixed=(25, (3., 3.), 500, 32, 1e-5), early=(40, (0.35, 0.3), 600, 64, 1e-5),
+                 fixed_reg=(25, (3., 3.), 500, 32, 1.0), early_reg=(40, (0.35, 0.3), 600, 64, 1.0))
+    for name, (max_len, goal, nsamp, hid, reg) in cases.items():
+        random.seed(9); np.random.seed(9); torch.manual_seed(9)
+        env = PointEnv(goal=np.array(goal, dtype=np.float32), max_episode_length=max_len)
+        policy = GaussianMLPPolicy(env.spec, hidden_sizes=(hid, hid))
+        vf = GaussianMLPValueFunction(env.spec, hidden_sizes=(hid, hid))
+        sampler = LocalSampler(agents=policy, envs=env, max_episode_length=max_len, n_workers=2)
+        if reg == 1e-5:
+            algo = TRPO(env.spec, policy, vf, sampler)  # every default of trpo.py:47-88
+        else:
+            algo = TRPO(env.spec, policy, vf, sampler, policy_optimizer=OptimizerWrapper(
+                (ConjugateGradientOptimizer, dict(max_constraint_value=0.01, hvp_reg_coeff=reg)), policy))
+        eps = sampler.obtain_samples(0, nsamp, policy.get_param_values())
+        out[name + '_cfg'] = np.array([max_len, goal[0], goal[1], hid, reg], np.float64)
+        out[name + '_policy_flat'] = flat_of(policy.state_dict(), '_module.')
+        out[name + '_vf_flat'] = flat_of(vf.state_dict(), 'module.')
+        out[name + '_obs'], out[name + '_act'] = eps.observations, eps.actions
+        out[name + '_rew'], out[name + '_lengths'] = eps.rewards, eps.lengths.astype(np.int64)
+        out[name + '_step_types'] = np.asarray(eps.step_types, dtype=np.uint8)
+        out[name + '_last_obs'] = eps.last_observations
+        out[name + '_success'] = eps.env_infos['success']
+        # ---- known answers of the optimiser's pieces at the initial parameters
+        obs = torch.from_numpy(np.asarray(eps.observations, np.float32))
+        params = [p for p in policy.parameters()]
+        rng = np.random.default_rng(4)
+        P = sum(p.numel() for p in params)
+        f_Ax = cgo._build_hessian_vector_product(lambda: algo._compute_kl_constraint(obs), params, reg)
+        vs = rng.standard_normal((3, P)).astype(np.float32)
+        out[name + '_hvp_vec'] = vs
+        out[name + '_hvp_out'] = np.stack([f_Ax(torch.from_numpy(v)).detach().numpy() for v in vs])
+        b = torch.from_numpy((rng.standard_normal(P) * 0.01).astype(np.float32))
+        out[name + '_cg_b'] = b.numpy().copy()
+        out[name + '_cg_x'] = cgo._conjugate_gradient(f_Ax, b, 10).detach().numpy()
+        np.random.seed(13)  # the value function's BatchDataset shuffles
+        ref_shims.tabular.clear()
+        # record (not alter) what the reference feeds its policy step and the gradient it starts from
+        orig_train_policy, rec = algo._train_policy, {}
+
+        def recording_train_policy(obs_, actions_, rewards_, advantages_):
+            rec['adv'] = advantages_.detach().numpy().copy()
+            rec['n'] = rec.get('n', 0) + 1
+            loss_ = orig_train_policy(obs_, actions_, rewards_, advantages_)
+            rec['grad'] = flat_grad_of(policy, '_module.')
+            return loss_
+        algo._train_policy = recording_train_policy
+        ret = algo._train_once(0, eps)
+        assert rec['n'] == 1  # full batch, one epoch (OptimizerWrapper defaults)
+        out[name + '_adv'] = rec['adv']
+        out[name + '_loss_grad'] = rec['grad']
+        out[name + '_return'] = np.float64(ret)
+        out[name + '_policy_flat_after'] = flat_of(policy.state_dict(), '_module.')
+        out[name + '_vf_flat_after'] = flat_of(vf.state_dict(), 'module.')
+        keys = sorted(ref_shims.tabular.data)
+        out[name + '_log_keys'] = np.array(keys)
+        out[name + '_log_vals'] = np.array([float(ref_shims.tabular.data[k]) for k in keys])
+        d = out[name + '_policy_flat_after'] - out[name + '_policy_flat']
+        print('trpo case', name, 'P', P, 'episodes', len(eps.lengths), 'steps', int(eps.lengths.sum()),
+              '|step|', float(np.abs(d).max()), 'KL', ref_shims.tabular.data.get('GaussianMLPPolicy/KL'))
+    np.savez_compressed(os.path.join(OUT, 'trpo.npz'), **out)
+
+
 def main():
     from oracle import ref_shims
     if not ref_shims.install():
@@ -316,6 +406,7 @@ def main():
     gen_losses()
     gen_train_once()
     gen_gridworld()
+    gen_trpo()
     for f in sorted(os.listdir(OUT)):
         print(f, os.path.getsize(os.path.join(OUT, f)))
 

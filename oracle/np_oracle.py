@@ -640,3 +640,96 @@ def gridworld_vec_rollout(cells, table, max_episode_length, n_envs, num_samples)
             else:
                 state[n] = nxt
     return {k: np.asarray(v) for k, v in out.items()}
+
+
+# ------------------------------------------------------------------- TRPO --
+def mlp_jvp(p, v, obs):
+    """Forward-mode derivative of the mean network: d mu / d theta . v for a tangent `v` given as
+    an unflattened parameter dict (what autograd's double-backward evaluates inside
+    torch/optimizers/conjugate_gradient_optimizer.py:18-66 for the mean parameters)."""
+    x = np.asarray(obs, np.float64)
+    mean, h1, h2 = mlp_forward(p, x)
+    dz1 = x @ v['W1'].T + v['b1']
+    dh1 = (1 - h1**2) * dz1
+    dz2 = dh1 @ p['W2'].T + h1 @ v['W2'].T + v['b2']
+    dh2 = (1 - h2**2) * dz2
+    return dh2 @ p['W3'].T + h2 @ v['W3'].T + v['b3'], h1, h2
+
+
+def fisher_vector_product(flat, O, H, A, obs, vec, reg_coeff=1e-5, min_std=1e-6, max_std=None):
+    """`_build_hessian_vector_product(f_constraint, params, reg_coeff)(vec)`
+    (conjugate_gradient_optimizer.py:18-66) with f_constraint = mean KL(old || new)
+    (torch/algos/vpg.py:381-406) evaluated where new == old (TRPO's full-batch step starts there,
+    trpo.py:119-144): the Hessian of the KL of two diagonal Gaussians with a state-independent
+    log-std is J^T diag(1/var) J / n on the mean parameters (the network's second-order term
+    multiplies mu_old - mu_new = 0) and 2 A on log_std (0 when the clamp blocks the gradient),
+    no cross term; plus reg_coeff * vec."""
+    p = unflatten_params(np.asarray(flat, np.float64), O, H, A)
+    v = unflatten_params(np.asarray(vec, np.float64), O, H, A)
+    n = np.asarray(obs).shape[0]
+    dmu, h1, h2 = mlp_jvp(p, v, obs)
+    ls, ls_pass = clamped_log_std(p, min_std, max_std)
+    var = math.exp(ls)**2
+    out = _mlp_backward(p, np.asarray(obs, np.float64), h1, h2, dmu / var / n, 0.0)
+    out[0] = 2.0 * A * float(v['log_std'][0]) if ls_pass else 0.0
+    return out + reg_coeff * np.asarray(vec, np.float64)
+
+
+def conjugate_gradient(f_Ax, b, cg_iters=10, residual_tol=1e-10):
+    """conjugate_gradient_optimizer.py:69-110 (Demmel p. 312), float64."""
+    b = np.asarray(b, np.float64)
+    p, r, x = b.copy(), b.copy(), np.zeros_like(b)
+    rdotr = r @ r
+    for _ in range(cg_iters):
+        z = f_Ax(p)
+        v = rdotr / (p @ z)
+        x += v * p
+        r -= v * z
+        newrdotr = r @ r
+        mu = newrdotr / rdotr
+        p = r + mu * p
+        rdotr = newrdotr
+        if rdotr < residual_tol:
+            break
+    return x
+
+
+def trpo_policy_step(flat, O, H, A, obs, act, adv, old_logp, old_mean, old_log_std,
+                     max_constraint_value=0.01, cg_iters=10, max_backtracks=15, backtrack_ratio=0.8,
+                     hvp_reg_coeff=1e-5, accept_violation=False):
+    """One `TRPO._train_policy` (trpo.py:119-144) = ConjugateGradientOptimizer.step
+    (conjugate_gradient_optimizer.py:141-260): loss gradient of -mean(ratio * adv)
+    (trpo.py:90-117), CG on the Fisher-vector product, step size sqrt(2 delta / (x^T A x + 1e-8)),
+    backtracking line search on (loss, mean KL(old || new)).  Returns (new flat, info)."""
+    flat = np.asarray(flat, np.float64)
+
+    def f_loss(theta):
+        return policy_loss_and_grad(theta, O, H, A, obs, act, adv, old_logp, kind='ppo', clip=np.inf)
+
+    def f_kl(theta):
+        p = unflatten_params(theta, O, H, A)
+        mean, _, _ = mlp_forward(p, obs)
+        ls, _ = clamped_log_std(p)
+        return float(kl_normal(np.asarray(old_mean, np.float64), float(old_log_std), mean, ls).mean())
+
+    loss_before, g = f_loss(flat)
+    f_Ax = lambda v: fisher_vector_product(flat, O, H, A, obs, v, hvp_reg_coeff)
+    step_dir = conjugate_gradient(f_Ax, g, cg_iters)
+    step_dir[np.isnan(step_dir)] = 0.0
+    step_size = np.sqrt(2.0 * max_constraint_value * (1.0 / (step_dir @ f_Ax(step_dir) + 1e-8)))
+    if np.isnan(step_size):
+        step_size = 1.0
+    descent = step_size * step_dir
+    new, loss, kl, used = flat, loss_before, 0.0, None
+    for k in range(max_backtracks):
+        ratio = backtrack_ratio**k
+        new = flat - ratio * descent
+        loss, kl = f_loss(new)[0], f_kl(new)
+        used = k
+        if loss < loss_before and kl <= max_constraint_value:
+            break
+    violated = (np.isnan(loss) or np.isnan(kl) or loss >= loss_before or kl >= max_constraint_value)
+    if violated and not accept_violation:
+        new = flat
+    return new, dict(loss_before=loss_before, loss=loss, kl=kl, backtracks=used, rejected=bool(violated and not accept_violation),
+                     grad=g, step_dir=step_dir, step_size=step_size)

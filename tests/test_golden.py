@@ -153,3 +153,56 @@ def test_gridworld_vecworker_restatement(k):
                                   int(c['num_samples']))
     for key in ('observations', 'actions', 'rewards', 'step_types', 'last_observations', 'lengths'):
         np.testing.assert_array_equal(got[key], c[key], err_msg=key)
+
+
+# ------------------------------------------------------------------ TRPO --
+TRPO_CASES = ['fixed', 'early', 'fixed_reg', 'early_reg']
+
+
+def _trpo_case(case):
+    d = load('trpo.npz')
+    hid, reg = int(d[case + '_cfg'][3]), float(d[case + '_cfg'][4])
+    flat, obs, act = d[case + '_policy_flat'], d[case + '_obs'], d[case + '_act']
+    p = O.unflatten_params(flat.astype(np.float64), 3, hid, 2)
+    mean, _, _ = O.mlp_forward(p, obs)
+    ls, _ = O.clamped_log_std(p)
+    old_logp = O.normal_log_prob(act.astype(np.float64), mean, ls)
+    return d, hid, reg, flat, obs, act, mean, ls, old_logp
+
+
+@pytest.mark.parametrize('case', TRPO_CASES)
+def test_trpo_pieces_vs_reference(case):
+    """Oracle restatement of the loss gradient (trpo.py:90-117) and of the Hessian-vector product of
+    the KL constraint (conjugate_gradient_optimizer.py:18-66) against the reference's autograd
+    (double backward) on its own batch: fixture oracle/gen_golden.py::gen_trpo."""
+    d, hid, reg, flat, obs, act, mean, ls, old_logp = _trpo_case(case)
+    _, g = O.policy_loss_and_grad(flat, 3, hid, 2, obs, act, d[case + '_adv'], old_logp, kind='ppo', clip=np.inf)
+    want = d[case + '_loss_grad'].astype(np.float64)
+    assert np.abs(g - want).max() <= 1e-5 * np.abs(want).max()
+    for v, w in zip(d[case + '_hvp_vec'], d[case + '_hvp_out']):
+        got = O.fisher_vector_product(flat, 3, hid, 2, obs, v, reg)
+        assert np.abs(got - w).max() <= 1e-5 * np.abs(w).max()
+
+
+@pytest.mark.parametrize('case', ['fixed_reg', 'early_reg'])
+def test_trpo_cg_and_step_vs_reference(case):
+    """Where the linear system is well conditioned (hvp_reg_coeff = 1) the reference's float32 CG, step
+    size and line search are reproducible: CG solution and the policy after `_train_policy`."""
+    d, hid, reg, flat, obs, act, mean, ls, old_logp = _trpo_case(case)
+    f_Ax = lambda v: O.fisher_vector_product(flat, 3, hid, 2, obs, v, reg)
+    x = O.conjugate_gradient(f_Ax, d[case + '_cg_b'])
+    assert np.abs(x - d[case + '_cg_x']).max() <= 1e-5 * np.abs(d[case + '_cg_x']).max()
+    new, info = O.trpo_policy_step(flat, 3, hid, 2, obs, act, d[case + '_adv'], old_logp, mean, ls,
+                                   hvp_reg_coeff=reg)
+    assert not info['rejected']
+    assert np.allclose(new, d[case + '_policy_flat_after'], rtol=1e-5, atol=2e-6)
+
+
+def test_trpo_default_config_is_ill_conditioned():
+    """Documents why the default-configuration cases pin pieces only: a float64 replay of the SAME
+    algorithm lands far from the reference's float32 step (CG with A ~ 1e-5 I in the null space of a
+    500-sample Fisher matrix amplifies rounding noise)."""
+    d, hid, reg, flat, obs, act, mean, ls, old_logp = _trpo_case('fixed')
+    new, _ = O.trpo_policy_step(flat, 3, hid, 2, obs, act, d['fixed_adv'], old_logp, mean, ls, hvp_reg_coeff=reg)
+    step = np.abs(d['fixed_policy_flat_after'] - flat).max()
+    assert np.abs(new - d['fixed_policy_flat_after']).max() > 0.1 * step

@@ -28,8 +28,17 @@ def make_case(Od, H, A, n, seed, scale=0.5):
     p = O.unflatten_params(flat.astype(np.float64), Od, H, A)
     mean, _, _ = O.mlp_forward(p, obs)
     ls, _ = O.clamped_log_std(p)
-    old_logp = (O.normal_log_prob(act.astype(np.float64), mean, ls) +
-                rng.standard_normal(n) * 0.3).astype(np.float32)
+    ll = O.normal_log_prob(act.astype(np.float64), mean, ls)
+    old_logp = (ll + rng.standard_normal(n) * 0.3).astype(np.float32)
+    # The clipped surrogate is discontinuous in its gradient at ratio = 1 +- clip (ppo.py:113-132): a row
+    # within float32 rounding of a boundary is clipped or not depending on the last bit of exp(), in the
+    # reference as much as here.  Keep every row of the synthetic cases 1e-4 away from both boundaries.
+    for _ in range(4):
+        ratio = np.exp(ll - old_logp.astype(np.float64))
+        near = np.minimum(np.abs(ratio - 0.8), np.abs(ratio - 1.2)) < 1e-4
+        if not near.any():
+            break
+        old_logp[near] += np.float32(0.01)
     ret = rng.standard_normal(n).astype(np.float32) * 3
     return flat, obs, act, adv, old_logp, ret
 
@@ -171,7 +180,7 @@ def test_adam_steps_match_oracle():
 def test_unsupported_shape_fails_loudly():
     from garage_b200 import ops
     with pytest.raises(NotImplementedError):
-        ops.MlpShape(5, 64, 1, torch.device('cuda:0'))
+        ops.MlpShape(9, 64, 1, torch.device('cuda:0'))  # obs_dim > 8 (general kernels: obs 1..8, out 1..4, hidden 32/64/128)
 
 
 @pytest.mark.parametrize('Od,A,n', [(3, 1, 64), (3, 2, 1000), (4, 1, 20001), (3, 1, 1)])
