@@ -102,6 +102,7 @@ SIGNATURES = {
     'b2g_mlp_train_loop_debug_timing': (c_int, [P, c_int]),
     'b2g_mlp_train_loop': (c_int, [POINTER(TrainNet), c_int, P, c_int64, P]),
     'b2g_train_comm_bytes': (c_int64, []),
+    'b2g_mlp_train_loop_kind': (c_int, [POINTER(TrainNet), c_int, c_int]),
     'b2g_mlp_train_loop_dist': (c_int, [POINTER(TrainNet), c_int, POINTER(TrainComm), P, c_int64, P]),
     'b2g_mlp_fvp': (c_int, [c_int, c_int, c_int, P, P, P, c_int64, c_int64, P, c_float, c_float, c_float, P, P, P, P]),
     'b2g_cg_init': (c_int, [P, P, P, P, P, c_int, P]),

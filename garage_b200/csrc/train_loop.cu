@@ -15,35 +15,9 @@
 // The minibatch shuffle is evaluated on the fly (b2g_perm_apply) or read from the supplied
 // index lists; weights, Adam moments and the step counter are updated in place.
 #include "mlp_tc.cuh"
+#include "train_loop_common.cuh"
 #include <stdlib.h>
 #include <string.h>
-
-struct NetLoop {
-    MlpArgs a;  // data pointers + loss configuration (params/idx/start/mb/partial are set per step)
-    float* params;
-    float* adam_m;
-    float* adam_v;
-    unsigned long long* step;
-    double lr, beta1, beta2, eps;
-    int64_t B, mbs;
-    int epochs, shuffle;  // shuffle: 0 sequential, 1 device permutation, 2 index lists [epochs][B]
-    const int32_t* idx_all;
-    uint32_t seed_lo, seed_hi;
-    float* partial;       // [ctas][P + MLP_NSTATS]
-    unsigned int* sync;   // barrier counter, zero at launch
-    // multi-GPU (one process per GPU): peer-mapped exchange buffers, see b2g_mlp_train_loop_dist
-    unsigned long long* peer_recv[B2G_MAX_RANKS];  // rank r's receive area of this network: [src rank][parity][COMM_P] slots
-    int world, rank;
-    unsigned int* seq_ptr;                  // device counter: minibatch steps this network has exchanged so far
-    long long* timing;    // debug: [ctas][16] clock64 stamps of minibatch step `timing_step` (or NULL)
-    long long* tile_timing;  // debug: [ctas][32] stage stamps of the tiles of that step
-    int timing_step;
-};
-struct LoopArgs {
-    NetLoop net[2];
-    int n_nets, ctas_per_net;
-    int stagger_cycles;  // the second network starts this many cycles late (see b2g_mlp_train_loop)
-};
 
 constexpr int COMM_P = 4608;  // per-network capacity of the exchange area (parameters)
 
@@ -119,31 +93,6 @@ __device__ __forceinline__ float slice_allreduce(const NetLoop& n, bool own, int
     for (int r = 0; r < B2G_MAX_RANKS; ++r)
         if (r < n.world) sum += v[r];
     return sum;
-}
-
-// Barrier over the CTAs of one network (all co-resident): arrive = one release-reduction (no reply
-// to wait for), wait = acquire loads until the count reaches `target`.  bar.sync orders the other
-// threads' writes before thread 0's release and thread 0's acquire before their later reads.
-// The two halves are separate calls so that work which does not depend on the other CTAs (the rows
-// of the next minibatch) runs between "my partial row is published" and "everybody's is".
-__device__ __forceinline__ void net_barrier_arrive(unsigned int* ctr) {
-    __syncthreads();
-    if (threadIdx.x == 0) asm volatile("red.release.gpu.global.add.u32 [%0], 1;" ::"l"(ctr) : "memory");
-}
-__device__ __forceinline__ void net_barrier_wait(unsigned int* ctr, unsigned int target) {
-    if (threadIdx.x == 0) {
-        unsigned int v;
-        unsigned int spin = 0;
-        do {
-            asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(ctr) : "memory");
-            if (++spin > (1u << 22)) __trap();  // a lost CTA must surface as an error, not as a hung GPU
-        } while (v < target);
-    }
-    __syncthreads();
-}
-__device__ __forceinline__ void net_barrier(unsigned int* ctr, unsigned int target) {
-    net_barrier_arrive(ctr);
-    net_barrier_wait(ctr, target);
 }
 
 template <int O, int A>
@@ -315,7 +264,8 @@ static size_t loop_smem() {
 }
 
 static int check_net(const b2g_train_net* t) {
-    B2G_CHECK_ARG(t->hidden == 64, "the fused training loop is built for hidden = (64, 64)");
+    B2G_CHECK_ARG(t->hidden == 32 || t->hidden == 64 || t->hidden == 128, "the fused training loop is built for hidden in {32, 64, 128}");
+    B2G_CHECK_ARG(t->obs_dim >= 1 && t->obs_dim <= 8 && t->out_dim >= 1 && t->out_dim <= 4, "obs_dim 1..8, out_dim 1..4");
     B2G_CHECK_ARG(t->params && t->adam_m && t->adam_v && t->step_counter && t->obs, "NULL pointer");
     B2G_CHECK_ARG(t->n_rows > 0 && t->epochs >= 0, "empty batch");
     B2G_CHECK_ARG(t->loss_kind >= LOSS_PPO && t->loss_kind <= LOSS_VF, "bad loss_kind");
@@ -355,9 +305,33 @@ static void fill_net(NetLoop& n, const b2g_train_net* t, int ctas, float* partia
 }
 
 extern "C" int64_t b2g_mlp_train_loop_ws_floats(void) {
-    // two networks x (2 SMs worth of CTAs) x (largest built parameter vector + statistics) + barrier counters
-    const int64_t P = MlpLayout{4, 64, 4}.total() + MLP_NSTATS;
+    // (2 CTAs per SM) x (largest built parameter vector + statistics) + barrier counters
+    const int64_t P = MlpLayout{8, 128, 4}.total() + MLP_NSTATS;
     return 2 * (int64_t)b2g_sm_count() * P + 64;
+}
+
+// general-shape loops (train_loop_general_h*.cu)
+int b2g_gen_loop_h32(int op, int ap, LoopArgs& args, int64_t max_mb, cudaStream_t s);
+int b2g_gen_loop_h64(int op, int ap, LoopArgs& args, int64_t max_mb, cudaStream_t s);
+int b2g_gen_loop_h128(int op, int ap, LoopArgs& args, int64_t max_mb, cudaStream_t s);
+extern "C" int b2g_get_mlp_path(void);
+static bool tc_loop_built(int O, int A) { return (O == 3 && A == 1) || (O == 3 && A == 2) || (O == 4 && A == 1); }
+
+// which loop runs these networks: 1 tcgen05 (hidden 64, built (obs, out) pairs, default MLP path), 2 general
+// CUDA-core loop (one hidden size for all networks, single GPU), 0 neither
+extern "C" int b2g_mlp_train_loop_kind(const b2g_train_net* nets, int n_nets, int world) {
+    if (!nets || n_nets < 1 || n_nets > 2) return 0;
+    bool tc = b2g_get_mlp_path() == 0;
+    for (int i = 0; i < n_nets; ++i) tc = tc && nets[i].hidden == 64;
+    tc = tc && tc_loop_built(nets[0].obs_dim, nets[0].out_dim) && (n_nets == 1 || nets[1].obs_dim == nets[0].obs_dim);
+    if (tc) return 1;
+    if (world > 1) return 0;
+    for (int i = 0; i < n_nets; ++i) {
+        const b2g_train_net& t = nets[i];
+        if (!(t.hidden == 32 || t.hidden == 64 || t.hidden == 128) || t.hidden != nets[0].hidden) return 0;
+        if (t.obs_dim < 1 || t.obs_dim > 8 || t.out_dim < 1 || t.out_dim > 4) return 0;
+    }
+    return 2;
 }
 
 template <int O, int AP>
@@ -535,6 +509,34 @@ extern "C" int b2g_mlp_train_loop_dist(const b2g_train_net* nets, int n_nets, co
         for (int r = 0; r < comm->world; ++r) B2G_CHECK_ARG(comm->peer_base[r] != nullptr, "NULL peer buffer");
     }
     cudaStream_t s = (cudaStream_t)stream;
+    const int kind = b2g_mlp_train_loop_kind(nets, n_nets, comm ? comm->world : 1);
+    if (kind == 0) {
+        b2g_set_error("b2g_mlp_train_loop: no fused loop for these networks (tcgen05: hidden 64, (obs, out) in {(3,1), (3,2), "
+                      "(4,1)}; general: one hidden size in {32, 64, 128}, obs 1..8, out 1..4, one GPU)");
+        return B2G_ERR_UNSUPPORTED;
+    }
+    if (kind == 2) {
+        LoopArgs args{};
+        args.n_nets = n_nets;
+        unsigned int* sync = reinterpret_cast<unsigned int*>(workspace);
+        B2G_CUDA(cudaMemsetAsync(sync, 0, 256, s));
+        int64_t max_mb = 1;
+        for (int i = 0; i < n_nets; ++i) {
+            fill_net(args.net[i], &nets[i], 0, workspace + 64, sync + 16 * i, i);
+            args.net[i].a.O_rt = nets[i].obs_dim;
+            args.net[i].a.A_rt = nets[i].out_dim;
+            args.net[i].timing = nullptr;
+            if (args.net[i].mbs > max_mb) max_mb = args.net[i].mbs;
+        }
+        const int op = nets[0].obs_dim <= 4 ? 4 : 8;
+        int amax = 1;
+        for (int i = 0; i < n_nets; ++i) amax = nets[i].out_dim > amax ? nets[i].out_dim : amax;
+        const int ap = amax <= 1 ? 1 : (amax == 2 ? 2 : 4);
+        B2G_CHECK_ARG(n_nets == 1 || nets[1].obs_dim <= op, "both networks read the same observations");
+        if (nets[0].hidden == 32) return b2g_gen_loop_h32(op, ap, args, max_mb, s);
+        if (nets[0].hidden == 64) return b2g_gen_loop_h64(op, ap, args, max_mb, s);
+        return b2g_gen_loop_h128(op, ap, args, max_mb, s);
+    }
     if (comm && comm->world > 1) {
         static bool timeout_set = false;
         if (!timeout_set) {

@@ -671,6 +671,14 @@ def line_search_point(prev, descent, ratio, params):
              _stream(prev))
 
 
+def train_loop_kind(shapes, world=1):
+    """b2g_mlp_train_loop_kind for MlpShape objects: 1 tcgen05 loop, 2 general CUDA-core loop, 0 none."""
+    arr = (_lib.TrainNet * len(shapes))()
+    for t, sh in zip(arr, shapes):
+        t.obs_dim, t.hidden, t.out_dim = sh.O, sh.H, sh.A
+    return int(_lib.load().b2g_mlp_train_loop_kind(arr, len(shapes), int(world)))
+
+
 def loop_shape_built(shape):
     """True when the tcgen05 fused training loop is compiled for this (obs, out) pair (hidden 64)."""
     return shape.H == 64 and (shape.O, shape.A) in ((3, 1), (3, 2), (4, 1))

@@ -58,8 +58,7 @@ class TRPO(VPG):
         """vpg.py:230-248 with trpo.py:119-144 as the policy step."""
         self._train_policy_cg(f)
         vf, opt = self._value_function, self._vf_optimizer
-        if (self._update_mode != 'stepwise' and self._world() == 1 and ops.mlp_path() == 0 and
-                ops.loop_shape_built(vf.mlp_shape)):
+        if self._update_mode != 'stepwise' and ops.mlp_path() != 1 and ops.train_loop_kind([vf.mlp_shape], self._world()):
             ops.mlp_train_loop([self._loop_net(opt, vf, f, False)])
         else:
             self._run_minibatches(opt, vf, f, policy=False)

@@ -403,14 +403,20 @@ class VPG(RLAlgorithm):
                 np.random.shuffle(host_ids)
 
     def _fused_applies(self):
+        """True when one persistent launch runs every minibatch step of both networks: the tcgen05 loop
+        (hidden 64, the built (obs, out) pairs; also multi-GPU) or the general CUDA-core loop (any built
+        shape with one hidden size, one GPU) -- b2g_mlp_train_loop_kind."""
         if self._update_mode == 'stepwise':
             return False
-        ok = (self.policy.mlp_shape.H == 64 and self._value_function.mlp_shape.H == 64 and
-              ops.mlp_path() == 0 and self._policy_optimizer.cg is None and self._vf_optimizer.cg is None and
-              ops.loop_shape_built(self.policy.mlp_shape) and ops.loop_shape_built(self._value_function.mlp_shape))
-        if not ok and self._update_mode == 'fused':
-            raise NotImplementedError("update_mode='fused' needs hidden sizes (64, 64) and the tcgen05 path")
-        return ok
+        adam = self._policy_optimizer.cg is None and self._vf_optimizer.cg is None
+        kind = ops.train_loop_kind([self.policy.mlp_shape, self._value_function.mlp_shape], self._world()) if adam else 0
+        if ops.mlp_path() == 1:
+            kind = 0  # B2G_MLP_PATH=ffma: the step-wise CUDA-core kernels are what the caller asked for
+        if not kind and self._update_mode == 'fused':
+            raise NotImplementedError("update_mode='fused': no fused loop for these networks (tcgen05: hidden 64 with "
+                                      "(obs, out) in {(3,1), (3,2), (4,1)}; general: one hidden size in {32, 64, 128}, "
+                                      "obs <= 8, out <= 4, one GPU)")
+        return bool(kind)
 
     def _loop_net(self, opt, module_owner, f, policy):
         """One network of the fused loop; draws the reference's BatchDataset shuffles here

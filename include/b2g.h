@@ -386,6 +386,12 @@ typedef struct b2g_train_net {
     const int32_t* idx;
 } b2g_train_net;
 int64_t b2g_mlp_train_loop_ws_floats(void);
+/* Which persistent loop b2g_mlp_train_loop[_dist] runs for these networks (only obs_dim / hidden / out_dim
+ * are read): 1 = tcgen05 tiles (hidden 64, (obs, out) in {(3,1), (3,2), (4,1)}, default MLP path; one or
+ * several GPUs), 2 = general CUDA-core tiles (one hidden size in {32, 64, 128} for all networks, obs 1..8,
+ * out 1..4; one GPU; the CTAs per network follow the minibatch, a 64-row minibatch runs on one CTA without
+ * device-wide barriers), 0 = none: the caller takes the step-wise path. */
+int b2g_mlp_train_loop_kind(const b2g_train_net* nets, int n_nets, int world);
 
 /* Multi-GPU form (one process per GPU, env-sharded data parallelism; the reference has no
  * counterpart).  Every rank runs the same loop on its own shard; per minibatch step the gradient

@@ -78,13 +78,101 @@ def test_fused_two_action_dims_pointenv():
     assert _rel(pf, ps) < 1e-5 and _rel(vf_, vs) < 1e-5
 
 
-def test_fused_refuses_other_hidden_sizes():
+def test_fused_refuses_mixed_hidden_sizes():
+    """No persistent loop is built for networks of different hidden sizes: 'fused' fails loudly, 'auto'
+    takes the step-wise path."""
     from garage_b200.envs import PendulumEnv
+    from garage_b200.sampler import GPUSampler
+    from garage_b200.torch.algos import PPO
+    from garage_b200.torch.policies import GaussianMLPPolicy
+    from garage_b200.torch.value_functions import GaussianMLPValueFunction
     env = PendulumEnv(max_episode_length=40)
-    a, policy, vf, sampler = build(env, hidden=(32, 32), n_envs=16, update_mode='fused')
+    policy = GaussianMLPPolicy(env.spec, hidden_sizes=(64, 64))
+    vf = GaussianMLPValueFunction(env.spec, hidden_sizes=(32, 32))
+    sampler = GPUSampler(policy, env, max_episode_length=40, n_envs=16, seed=3)
+    a = PPO(env.spec, policy, vf, sampler, update_mode='fused')
     eps = sampler.obtain_samples(0, 16 * 40, policy)
     with pytest.raises(NotImplementedError):
         a._train_once(0, eps)
+    b = PPO(env.spec, policy, vf, sampler)
+    assert not b._fused_applies()
+    assert np.isfinite(b._train_once(0, eps))
+
+
+@pytest.mark.parametrize('hidden', [(32, 32), (128, 128)])
+@pytest.mark.parametrize('env_name,mb', [('pendulum', 64), ('pendulum', 1000), ('point', 64), ('cartpole', 700), ('pendulum', None)])
+def test_general_fused_loop_matches_stepwise(hidden, env_name, mb):
+    """The general-shape persistent loop (train_loop_general_*.cu: hidden 32 / 128, one CTA per network
+    for 64-row minibatches, several with device-wide barriers for larger ones) against the step-wise
+    kernels on the same data, shuffles and Adam state."""
+    from garage_b200.envs import CartPoleEnv, PendulumEnv, PointEnv
+    cls = dict(pendulum=PendulumEnv, point=PointEnv, cartpole=CartPoleEnv)[env_name]
+    if hidden == (128, 128):
+        pytest.skip('the device sampler is built for hidden 32 / 64; hidden 128 is covered on host batches below')
+    kw = dict(seed_np=5, shuffle='numpy') if env_name == 'cartpole' else {}
+    pf, vf_, sf, lf = _run(cls, 'ppo', 'fused', 64, 2, mb, hidden=hidden, **kw)
+    ps, vs, ss, ls = _run(cls, 'ppo', 'stepwise', 64, 2, mb, hidden=hidden, **kw)
+    assert sf == ss and sf[0] > 0
+    assert _rel(pf, ps) < 1e-5 and _rel(vf_, vs) < 1e-5
+    for k in ('GaussianMLPPolicy/LossAfter', 'GaussianMLPPolicy/KL', 'GaussianMLPValueFunction/LossAfter'):
+        assert abs(lf[k] - ls[k]) <= 1e-5 * max(1.0, abs(ls[k])) + 1e-7, k
+
+
+@pytest.mark.parametrize('Od,H,A', [(6, 128, 3), (8, 32, 4), (5, 64, 2), (3, 32, 2)])
+@pytest.mark.parametrize('mb', [64, 300, None])
+def test_general_fused_loop_vs_oracle_adam_sequence(Od, H, A, mb):
+    """Policy (PPO) + value function through the general persistent loop on supplied index lists vs the
+    float64 oracle replaying forward / backward / Adam on the same rows (2 epochs)."""
+    from garage_b200 import ops
+    from oracle import np_oracle as O
+    from tests.test_mlp_gpu import make_case
+    import math
+    B, E = 777, 2
+    flat, obs, act, adv, old_logp, ret = make_case(Od, H, A, B, seed=Od + H + A)
+    vflat = make_case(Od, H, 1, 8, seed=H)[0]
+    dev = torch.device('cuda:0')
+    t = lambda x: torch.from_numpy(np.ascontiguousarray(x)).to(dev)
+    rng = np.random.default_rng(1)
+    ids = np.stack([rng.permutation(B) for _ in range(E)]).astype(np.int32)
+
+    def net(sh, f0, policy):
+        d = dict(shape=sh, params=t(f0.copy()), adam_m=torch.zeros(sh.P, device=dev), adam_v=torch.zeros(sh.P, device=dev),
+                 step_counter=torch.zeros(1, dtype=torch.int64, device=dev), lr=2.5e-4, beta1=0.9, beta2=0.999, eps=1e-8,
+                 obs=t(obs), minibatch=mb, epochs=E)
+        if policy:
+            d.update(act=t(act), adv=t(adv), old_logp=t(old_logp), loss_kind=ops.LOSS_PPO, min_log_std=math.log(1e-6))
+        else:
+            d.update(ret=t(ret), loss_kind=ops.LOSS_VF)
+        if mb is not None:
+            d.update(shuffle=ops.SHUFFLE_IDS, idx=t(ids))
+        return d
+    prev = ops.mlp_path()
+    try:
+        ops.set_mlp_path(3)  # (5, 64, 2) etc. must not fall to the tcgen05 loop
+        pol, vf = net(ops.MlpShape(Od, H, A, dev), flat, True), net(ops.MlpShape(Od, H, 1, dev), vflat, False)
+        assert ops.train_loop_kind([pol['shape'], vf['shape']]) == 2
+        ops.mlp_train_loop([pol, vf])
+        torch.cuda.synchronize()
+    finally:
+        ops.set_mlp_path(prev)
+    f32 = np.float32
+    op, om, ov = flat.copy(), np.zeros_like(flat), np.zeros_like(flat)
+    vp, vm, vv = vflat.copy(), np.zeros_like(vflat), np.zeros_like(vflat)
+    step = 0
+    size = mb or B
+    for e in range(E):
+        for s0 in range(0, B, size):
+            rows = ids[e, s0:s0 + size] if mb is not None else np.arange(B)
+            step += 1
+            _, g = O.policy_loss_and_grad(op, Od, H, A, obs[rows], act[rows], adv[rows], old_logp[rows])
+            op, om, ov = O.adam_step(op, g.astype(f32), om, ov, step)
+            _, g = O.vf_loss_and_grad(vp, Od, H, obs[rows], ret[rows])
+            vp, vm, vv = O.adam_step(vp, g.astype(f32), vm, vv, step)
+    assert int(pol['step_counter'].item()) == step == int(vf['step_counter'].item())
+    for netd, wp in ((pol, op), (vf, vp)):
+        got = netd['params'].cpu().numpy()
+        close = np.isclose(got, wp, rtol=1e-5, atol=2e-6)
+        assert close.mean() > 0.995 and np.abs(got - wp).max() <= 2 * 2.5e-4 * step
 
 
 def test_fused_matches_oracle_adam_sequence():
