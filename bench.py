@@ -644,10 +644,23 @@ def make_step(a, algo, policy, sampler, B):
     return step
 
 
-def make_e2e_step(algo, policy, sampler, B, io):
+def make_e2e_step(a, algo, policy, sampler, B, io):
     """The call a user makes, with HOST buffers: parameters in (pinned, H2D), EpisodeBatch + logging
-    scalars + updated parameters out (D2H)."""
+    scalars + updated parameters out (D2H).  With graphs enabled the public
+    `GraphedIteration(algo, B, host_params=...)` replays the same work -- copies included -- as one
+    CUDA graph and waits once per iteration; --no-graph runs it as eager API calls."""
     host_sd = {k: v.detach().cpu().pin_memory() for k, v in policy.state_dict().items()}
+    if not a.no_graph:
+        from garage_b200.torch.algos.graphed import GraphedIteration
+        runner = GraphedIteration(algo, B, warmup=2, host_params=host_sd)
+
+        def graphed_step(i):
+            ret = runner.run(i)
+            eps = runner.eps
+            _ = (eps.observations, eps.actions, eps.rewards, eps.lengths)  # numpy views of the pinned batch
+            io['h2d'], io['d2h'] = runner.h2d_bytes, runner.d2h_bytes
+            return ret
+        return graphed_step
 
     def e2e_step(i):
         eps = sampler.obtain_samples(i, B, host_sd)            # H2D: policy parameters
@@ -681,7 +694,7 @@ def measure(a, algo, policy, sampler, B, world, device, barrier, steps, warmup, 
     out = dict(ms_total=ms, per=per, warm_iters=wk)
     if with_e2e:
         io = dict(h2d=0, d2h=0)
-        e2e_step = make_e2e_step(algo, policy, sampler, B, io)
+        e2e_step = make_e2e_step(a, algo, policy, sampler, B, io)
         warm(e2e_step, max(warmup, 3), at_least=10)
         ems, eper = timed(e2e_step, steps, barrier)
         out.update(e2e_ms_total=max_over_ranks(ems, world, device)[0],

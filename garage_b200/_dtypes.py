@@ -446,7 +446,8 @@ class DeviceEpisodeBatch(EpisodeBatch):
         """NumPy view of a prefetched field, or a synchronous copy."""
         pinned = getattr(self, '_pinned', None)
         if pinned and name in pinned:
-            self._pinned_event.synchronize()
+            if self._pinned_event is not None:  # None: copies replayed by a CUDA graph, the caller synchronised
+                self._pinned_event.synchronize()
             return pinned[name].numpy()
         return getattr(self.dev, name).cpu().numpy()
 

@@ -17,7 +17,7 @@ class GraphedIteration:
         warmup (int): eager iterations before capture (lazy allocations, module loading).
     """
 
-    def __init__(self, algo, batch_size, warmup=1):
+    def __init__(self, algo, batch_size, warmup=1, host_params=None):
         env = algo._sampler._env
         if not getattr(env, 'never_terminates', False):
             raise ValueError('GraphedIteration needs static shapes: an env that only ends at '
@@ -34,11 +34,39 @@ class GraphedIteration:
         self._warmup = warmup
         self._eager_done = 0
         self.eps = None  # the (static) DeviceEpisodeBatch of the captured iteration
+        # host I/O inside the graph (the end-to-end form of an iteration): `host_params` is a dict of PINNED
+        # CPU tensors with the policy's state_dict keys -- copied H2D at the start of every replay (the
+        # sampler's agent_update), overwritten with the updated parameters at its end; the EpisodeBatch
+        # fields and the logging scalars land in pinned buffers too (DeviceEpisodeBatch.prefetch_host)
+        self._host_params = host_params
+        self._stats_host = None
+        self.h2d_bytes = self.d2h_bytes = 0
+        if host_params is not None:
+            for k, v in host_params.items():
+                if v.is_cuda or not v.is_pinned():
+                    raise ValueError('host_params[{!r}] must be a pinned CPU tensor'.format(k))
 
     def _enqueue(self):
         a = self._algo
+        hp = self._host_params
+        if hp is not None:  # H2D: this iteration's policy parameters (what `agent_update` carries)
+            sd = a.policy.state_dict()
+            for k, v in hp.items():
+                sd[k].copy_(v, non_blocking=True)
+            self.h2d_bytes = sum(v.numel() * v.element_size() for v in hp.values())
         eps = a._sampler.obtain_samples(0, self._batch_size, a.policy)
+        d2h = eps.prefetch_host() if hp is not None else 0  # D2H: the EpisodeBatch (side stream, pinned)
         stats, B, n_eps = a._enqueue_iteration(eps)
+        if hp is not None:
+            if self._stats_host is None:
+                self._stats_host = torch.empty(stats.shape, dtype=stats.dtype, pin_memory=True)
+            self._stats_host.copy_(stats, non_blocking=True)        # D2H: logging scalars
+            sd = a.policy.state_dict()
+            for k, v in hp.items():                                  # D2H: updated parameters
+                v.copy_(sd[k], non_blocking=True)
+            cur = torch.cuda.current_stream(stats.device)
+            cur.wait_event(eps._pinned_event)                        # join the side stream (graph capture needs it)
+            self.d2h_bytes = d2h + stats.numel() * stats.element_size() + self.h2d_bytes
         return eps, stats, B, n_eps
 
     def enqueue(self):
@@ -49,6 +77,8 @@ class GraphedIteration:
             with torch.cuda.graph(g):
                 self.eps, self._stats, B, n_eps = self._enqueue()
             self._graph, self._meta = g, (B, n_eps)
+            if self._host_params is not None:
+                self.eps._pinned_event = None  # a captured event cannot be waited on: run() synchronises the stream
         if self._graph is not None:
             self._graph.replay()
             return self._stats
@@ -61,4 +91,7 @@ class GraphedIteration:
         stats = self.enqueue()
         B, n_eps = self._meta
         self._algo._sampler.total_env_steps += 0  # already counted by obtain_samples when eager
+        if self._host_params is not None:
+            torch.cuda.current_stream(stats.device).synchronize()  # the one host wait of the iteration
+            return self._algo._log_iteration(itr, self._stats_host.numpy(), B, n_eps)
         return self._algo._log_iteration(itr, stats.cpu().numpy(), B, n_eps)

@@ -224,3 +224,36 @@ def test_ppo_loss_before_without_forward_pass():
     v._evaluate(fv, o1, before=True)
     v._evaluate(fv, o2, before=False)
     assert torch.equal(o1, o2) and o1[2].item() != 0.0  # same forward pass either way (entropy sum present)
+
+
+def test_graphed_iteration_with_host_io_equals_eager_api():
+    """`GraphedIteration(algo, B, host_params=...)`: one CUDA graph holds the H2D copy of the policy
+    parameters, the whole iteration and the D2H copies (EpisodeBatch, logging scalars, updated
+    parameters).  Same bits as the eager public-API sequence obtain_samples(host state_dict) ->
+    _train_once -> state_dict, iteration after iteration."""
+    from garage_b200.envs import PendulumEnv
+    from garage_b200.torch.algos.graphed import GraphedIteration
+    B = 64 * 40
+
+    def make():
+        a, policy, vf, sampler = build(PendulumEnv(max_episode_length=40), n_envs=64, epochs=2, mb=512, shuffle='device')
+        host = {k: v.detach().cpu().pin_memory() for k, v in policy.state_dict().items()}
+        return a, policy, sampler, host
+    a1, p1, s1, h1 = make()
+    eager_rets, eager_obs = [], None
+    for it in range(5):
+        eps = s1.obtain_samples(it, B, h1)
+        eps.prefetch_host()
+        eager_rets.append(a1._train_once(it, eps))
+        eager_obs = np.array(eps.observations)
+        for k, v in p1.state_dict().items():
+            h1[k].copy_(v)
+    a2, p2, s2, h2 = make()
+    runner = GraphedIteration(a2, B, warmup=2, host_params=h2)
+    graph_rets = [runner.run(it) for it in range(5)]
+    assert runner._graph is not None and runner.h2d_bytes > 0 and runner.d2h_bytes > B * 4 * 3
+    assert graph_rets == eager_rets
+    for k in h1:
+        assert torch.equal(h1[k], h2[k]), k
+    assert np.array_equal(np.asarray(runner.eps.observations), eager_obs)
+    assert torch.equal(p1.flat, p2.flat)
