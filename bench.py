@@ -593,9 +593,26 @@ def c3_record(device, n_envs=16384, horizon=200, iters=5):
         return dict(error=repr(e))
 
 
+_clean_buf = None
+
+
+def flush_l2_clean():
+    """flush_l2() (write 256 MB) followed by a read of another 256 MB: the L2 then holds CLEAN lines of
+    a foreign buffer.  After the write alone it holds 126 MB of dirty lines, and a short kernel measured
+    right behind it pays for writing them back (every miss evicts one): +2..8 us on the 25..50 us GAE
+    launches (tools/gae_tune.py), traffic that is not the kernel's."""
+    import torch
+    global _clean_buf
+    flush_l2()
+    if _clean_buf is None:
+        _clean_buf = torch.zeros(64 << 20, dtype=torch.float32, device='cuda')
+    _clean_buf.sum()
+
+
 def c5_sweep(device):
     """BASELINE configs[4]: standalone GAE / discounted-return sweep, gamma 0.99, lambda 0.95, 1 % of
-    the steps terminal, L2 flushed before every launch, median of 7; 17 algorithmic B per element."""
+    the steps terminal, L2 flushed (written, then read: clean lines) before every launch, median of 7;
+    17 algorithmic B per element."""
     import torch
     from garage_b200 import ops
     hbm, _, kind = peaks()
@@ -614,7 +631,7 @@ def c5_sweep(device):
                 adv, ret = torch.empty_like(rew), torch.empty_like(rew)
                 ts = []
                 for i in range(9):
-                    flush_l2()
+                    flush_l2_clean()
                     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
                     e0.record()
                     ops.gae_time_major(rew, val, st, None, discount=0.99, gae_lambda=0.95, adv_out=adv, ret_out=ret)
@@ -626,7 +643,8 @@ def c5_sweep(device):
                 gbs = 17.0 * T * N / (ms * 1e-3) / 1e9
                 rows.append(dict(T=T, N=N, us=ms * 1e3, gbs=gbs, frac=gbs / hbm))
                 del rew, val, st, adv, ret
-        return dict(peak_gbs=hbm, peak_kind=kind, p_done=0.01, l2='flushed before every launch', rows=rows)
+        return dict(peak_gbs=hbm, peak_kind=kind, p_done=0.01,
+                    l2='flushed before every launch: 256 MB written, then 256 MB read (clean lines)', rows=rows)
     except Exception as e:
         return dict(error=repr(e), rows=rows)
 

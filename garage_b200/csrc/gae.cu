@@ -5,6 +5,7 @@
 //   (r 4 + V 4 + step_type 1 read, A 4 + R 4 written).
 #include "common.cuh"
 #include <stdlib.h>
+#include <stdio.h>
 
 // ------------------------------------------------------ time-major kernel --
 // One thread per environment column n, sequential over t (the recurrence), the
@@ -232,7 +233,11 @@ template <int U>
 static int launch_time_major(const float* rew, const float* val, const uint8_t* st,
                              const float* last_val, float gamma, float lam, float* adv,
                              float* ret, int T, int64_t N, cudaStream_t s) {
-    const int threads = (N >= 148 * 256) ? 256 : (N >= 148 * 64 ? 64 : 32);
+    // CTA size: the columns are independent (no shared memory), so small CTAs cost nothing and spread evenly --
+    // with 256-thread CTAs N = 65,536 is 256 CTAs on 148 SMs (2 on some, 1 on others: the kernel runs as long
+    // as the 2-CTA SMs); aim for >= 6 CTAs per SM
+    const int64_t sms = b2g_sm_count();
+    const int threads = (N >= sms * 256 * 6) ? 256 : (N >= sms * 128 * 6 ? 128 : (N >= sms * 64 * 6 ? 64 : 32));
     const unsigned blocks = (unsigned)((N + threads - 1) / threads);
     const float gl = gamma * lam;
 #define B2G_GAE_LAUNCH(ST, A, R)                                                          \
@@ -262,14 +267,35 @@ extern "C" int b2g_gae_time_major(const float* rew, const float* val,
     cudaStream_t s = (cudaStream_t)stream;
     // few envs, long enough in time: split time over the warps of a CTA (env B2G_GAE_SPLIT=0 turns it off)
     if (T >= 64 && gae_split_enabled()) {
-        if (N <= 4096) return launch_time_split<32, 16>(rew, val, step_type, last_val, gamma, lam, adv_out, ret_out, T, N, s);
+        // experiment hook: B2G_GAE_FORCE="L,W" forces one split configuration for every shape
+        static int force = -1;
+        if (force < 0) {
+            const char* e = getenv("B2G_GAE_FORCE");
+            force = 0;
+            if (e) {
+                int l = 0, w = 0;
+                if (sscanf(e, "%d,%d", &l, &w) == 2) force = l * 100 + w;
+            }
+        }
+#define B2G_SPLIT(LL, WW) return launch_time_split<LL, WW>(rew, val, step_type, last_val, gamma, lam, adv_out, ret_out, T, N, s)
+        if (force == 3216) B2G_SPLIT(32, 16);
+        if (force == 1608) B2G_SPLIT(16, 8);
+        if (force == 1616) B2G_SPLIT(16, 16);
+        if (force == 816) B2G_SPLIT(8, 16);
+        if (force == 832) B2G_SPLIT(8, 32);
+        if (force == 1632) B2G_SPLIT(16, 32);
+        if (force == 432) B2G_SPLIT(4, 32);
+        if (force == 1) goto sequential;
+        if (N <= 4096) B2G_SPLIT(32, 16);
         static int64_t split_n = -1;
         if (split_n < 0) {
             const char* e = getenv("B2G_GAE_SPLIT_N");
             split_n = e ? atoll(e) : (1 << 15);
         }
-        if (N < split_n) return launch_time_split<16, 8>(rew, val, step_type, last_val, gamma, lam, adv_out, ret_out, T, N, s);
+        if (N < split_n) B2G_SPLIT(16, 8);
+#undef B2G_SPLIT
     }
+sequential:
     // bytes in flight ~ N * U * 9: aim for >= ~6 MB (HBM latency x bandwidth)
     if (N >= (1 << 17)) return launch_time_major<4>(rew, val, step_type, last_val, gamma, lam, adv_out, ret_out, T, N, s);
     if (N >= (1 << 16)) return launch_time_major<8>(rew, val, step_type, last_val, gamma, lam, adv_out, ret_out, T, N, s);
