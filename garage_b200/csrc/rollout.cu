@@ -12,8 +12,12 @@
 // float4 (G LDS.128 feed 4*G*H/32 FMAs).  Lanes 0..G-1 additionally own one env
 // each: state (float64) in registers, Philox4x32-10 counter RNG keyed by
 // (seed; global env id, global step), outputs written time-major [T,N].
+// WS form (hidden 128, where W2's rows no longer fit in registers): W2 stays resident in shared memory
+// (row stride H + 4 floats: the lanes' LDS.128 of one column group fall in distinct banks) and is
+// re-read per step next to the broadcast activations: UPL + G LDS.128 feed 4 G UPL FMAs.
 #include "envs.cuh"
 #include "mlp.cuh"
+#include <cstdlib>
 
 // tanh x = 1 - 2 / (1 + e^{2x}) on the SFU (ex2 / rcp), absolute error ~2e-7: the same activation
 // the tensor-core update kernels evaluate (mlp_tc.cuh), a quarter of tanhf's instructions.  The
@@ -53,7 +57,7 @@ struct RolloutArgs {
 
 constexpr int RO_WARPS = 4;
 
-template <int ENV, int H, int G, bool NORM>
+template <int ENV, int H, int G, bool NORM, bool WS = false>
 __global__ void __launch_bounds__(RO_WARPS * 32)
 rollout_kernel(const RolloutArgs a) {
     constexpr int O = EnvDims<ENV>::O, A = EnvDims<ENV>::A, S = EnvDims<ENV>::S;
@@ -65,18 +69,24 @@ rollout_kernel(const RolloutArgs a) {
     const MlpLayout L{O, H, A};
 
     __shared__ __align__(16) float sh_h[RO_WARPS][G][H];
-    __shared__ float sh_w[H * (H + 1)];  // padded staging: coalesced global read, conflict-free rows
+    // padded staging: coalesced global read, conflict-free rows (WS: resident for the whole kernel)
+    constexpr int WSTR = WS ? H + 4 : H + 1;
+    __shared__ float sh_w_static[WS ? 1 : H * (H + 1)];
+    extern __shared__ __align__(16) float sh_w_dyn[];
+    float* const sh_w = WS ? sh_w_dyn : sh_w_static;
 
     // ---- weights -> registers (W2 through smem so that global reads coalesce)
-    float w1[UPL][O], b1[UPL], w2[UPL][H], b2[UPL], w3[A][UPL], b3[A];
+    float w1[UPL][O], b1[UPL], w2[WS ? 1 : UPL][WS ? 1 : H], b2[UPL], w3[A][UPL], b3[A];
     for (int i = threadIdx.x; i < H * H; i += blockDim.x)
-        sh_w[(i / H) * (H + 1) + (i % H)] = a.policy[L.off_w2() + i];
+        sh_w[(i / H) * WSTR + (i % H)] = a.policy[L.off_w2() + i];
     __syncthreads();
+    if constexpr (!WS) {
 #pragma unroll
-    for (int u = 0; u < UPL; ++u) {
-        const int j = lane + 32 * u;
+        for (int u = 0; u < UPL; ++u) {
+            const int j = lane + 32 * u;
 #pragma unroll
-        for (int k = 0; k < H; ++k) w2[u][k] = sh_w[j * (H + 1) + k];
+            for (int k = 0; k < H; ++k) w2[u][k] = sh_w[j * WSTR + k];
+        }
     }
 #pragma unroll
     for (int u = 0; u < UPL; ++u) {
@@ -145,17 +155,23 @@ rollout_kernel(const RolloutArgs a) {
         for (int g = 0; g < G; ++g)
 #pragma unroll
             for (int u = 0; u < UPL; ++u) acc[g][u] = b2[u];
-#pragma unroll
+#pragma unroll(WS ? 4 : H / 4)
         for (int k4 = 0; k4 < H / 4; ++k4) {
+            float4 wv[UPL];
+#pragma unroll
+            for (int u = 0; u < UPL; ++u) {
+                if constexpr (WS) wv[u] = *reinterpret_cast<const float4*>(&sh_w[(lane + 32 * u) * WSTR + 4 * k4]);
+                else wv[u] = make_float4(w2[u][4 * k4 + 0], w2[u][4 * k4 + 1], w2[u][4 * k4 + 2], w2[u][4 * k4 + 3]);
+            }
 #pragma unroll
             for (int g = 0; g < G; ++g) {
                 const float4 hv = *reinterpret_cast<const float4*>(&sh_h[wib][g][4 * k4]);
 #pragma unroll
                 for (int u = 0; u < UPL; ++u) {
-                    acc[g][u] = fmaf(w2[u][4 * k4 + 0], hv.x, acc[g][u]);
-                    acc[g][u] = fmaf(w2[u][4 * k4 + 1], hv.y, acc[g][u]);
-                    acc[g][u] = fmaf(w2[u][4 * k4 + 2], hv.z, acc[g][u]);
-                    acc[g][u] = fmaf(w2[u][4 * k4 + 3], hv.w, acc[g][u]);
+                    acc[g][u] = fmaf(wv[u].x, hv.x, acc[g][u]);
+                    acc[g][u] = fmaf(wv[u].y, hv.y, acc[g][u]);
+                    acc[g][u] = fmaf(wv[u].z, hv.z, acc[g][u]);
+                    acc[g][u] = fmaf(wv[u].w, hv.w, acc[g][u]);
                 }
             }
         }
@@ -242,21 +258,31 @@ rollout_kernel(const RolloutArgs a) {
     }
 }
 
-template <int ENV, int H>
-static int launch_rollout(const RolloutArgs& a, cudaStream_t s) {
-    // pick G (envs per warp) so that one wave of resident warps (~8 per SM at
-    // ~220 registers) covers N when possible
-    const int64_t cap = (int64_t)b2g_sm_count() * 8;
+template <int ENV, int H, bool WS>
+static int launch_rollout_ws(const RolloutArgs& a, cudaStream_t s) {
+    // pick G (envs per warp) so that one wave of resident warps covers N when possible: ~8 warps per SM
+    // at ~220 registers with W2 in registers, 12 (three 4-warp CTAs of 66 KB) with W2 in shared memory
+    const int64_t cap = (int64_t)b2g_sm_count() * (WS ? 12 : 8);
     int G = 8;
     if (a.N <= cap) G = 1;
     else if (a.N <= cap * 2) G = 2;
     else if (a.N <= cap * 4) G = 4;
+    if (const char* e = getenv("B2G_RO_G")) {  // experiment hook (tools/rollout_time.py)
+        const int g = atoi(e);
+        if (g == 1 || g == 2 || g == 4 || g == 8) G = g;
+    }
+    constexpr size_t dyn = WS ? sizeof(float) * H * (H + 4) : 0;
+#define B2G_RO_K(GG, NN)                                                             \
+    {                                                                                \
+        auto k = rollout_kernel<ENV, H, GG, NN, WS>;                                 \
+        if (WS) B2G_CUDA(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dyn)); \
+        k<<<blocks, RO_WARPS * 32, dyn, s>>>(a);                                     \
+    }
 #define B2G_RO(GG)                                                                   \
     {                                                                                \
         const int64_t warps = (a.N + GG - 1) / GG;                                   \
         const unsigned blocks = (unsigned)((warps + RO_WARPS - 1) / RO_WARPS);       \
-        if (norm_active(a.Q)) rollout_kernel<ENV, H, GG, true><<<blocks, RO_WARPS * 32, 0, s>>>(a);  \
-        else rollout_kernel<ENV, H, GG, false><<<blocks, RO_WARPS * 32, 0, s>>>(a);  \
+        if (norm_active(a.Q)) B2G_RO_K(GG, true) else B2G_RO_K(GG, false)            \
     }
     switch (G) {
         case 1: B2G_RO(1); break;
@@ -265,8 +291,19 @@ static int launch_rollout(const RolloutArgs& a, cudaStream_t s) {
         default: B2G_RO(8); break;
     }
 #undef B2G_RO
+#undef B2G_RO_K
     B2G_CHECK_LAUNCH();
     return B2G_OK;
+}
+
+template <int ENV, int H>
+static int launch_rollout(const RolloutArgs& a, cudaStream_t s) {
+    if constexpr (H > 64) {
+        return launch_rollout_ws<ENV, H, true>(a, s);
+    } else {
+        static const bool ws = [] { const char* e = getenv("B2G_RO_WS"); return e && atoi(e) != 0; }();
+        return ws ? launch_rollout_ws<ENV, H, true>(a, s) : launch_rollout_ws<ENV, H, false>(a, s);
+    }
 }
 
 extern "C" int b2g_rollout(int env_id, const double* params, int max_episode_length,
@@ -297,8 +334,8 @@ extern "C" int b2g_rollout_norm(int env_id, const double* params, const b2g_norm
     B2G_CHECK_ARG(env_params_from_host(env_id, params, max_episode_length, &a.P), "bad env_id or params");
     B2G_CHECK_ARG(norm_from_host(norm, &a.Q), "normalize_obs / normalize_reward need the stats buffer");
     B2G_CHECK_ARG(n_steps >= 0 && N >= 0, "negative shape");
-    if (hidden != 32 && hidden != 64) {
-        b2g_set_error("b2g_rollout: hidden_sizes=(%d,%d) not built (supported: (32,32), (64,64))", hidden, hidden);
+    if (hidden != 32 && hidden != 64 && hidden != 128) {
+        b2g_set_error("b2g_rollout: hidden_sizes=(%d,%d) not built (supported: (32,32), (64,64), (128,128))", hidden, hidden);
         return B2G_ERR_UNSUPPORTED;
     }
     if (n_steps == 0 || N == 0) return B2G_OK;
@@ -312,7 +349,7 @@ extern "C" int b2g_rollout_norm(int env_id, const double* params, const b2g_norm
     a.mean = mean; a.success = success; a.last_obs = last_obs; a.ep_len = ep_len;
     cudaStream_t s = (cudaStream_t)stream;
 #define B2G_ENVH(E)                                                           \
-    (hidden == 32 ? launch_rollout<E, 32>(a, s) : launch_rollout<E, 64>(a, s))
+    (hidden == 32 ? launch_rollout<E, 32>(a, s) : hidden == 64 ? launch_rollout<E, 64>(a, s) : launch_rollout<E, 128>(a, s))
     switch (env_id) {
         case B2G_ENV_POINT: return B2G_ENVH(B2G_ENV_POINT);
         case B2G_ENV_PENDULUM: return B2G_ENVH(B2G_ENV_PENDULUM);

@@ -96,6 +96,9 @@ def test_point_env_reference_unit_cases():
 @pytest.mark.parametrize('name,H,N,T,max_len', [
     ('pendulum', 64, 300, 50, 20), ('pendulum', 32, 33, 30, 200), ('cartpole', 64, 1500, 120, 60),
     ('point', 32, 700, 60, 25), ('point_bonus', 64, 5000, 40, 40), ('cartpole', 32, 10000, 64, 500),
+    # hidden 128: W2 resident in shared memory; N picks 1, 2, 4 and 8 environments per warp
+    ('pendulum', 128, 300, 40, 20), ('cartpole', 128, 3000, 40, 30), ('point', 128, 6000, 30, 25),
+    ('pendulum', 128, 9001, 24, 10),
 ])
 def test_rollout_replay_parity(name, H, N, T, max_len):
     from garage_b200 import ops

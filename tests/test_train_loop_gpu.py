@@ -107,8 +107,6 @@ def test_general_fused_loop_matches_stepwise(hidden, env_name, mb):
     kernels on the same data, shuffles and Adam state."""
     from garage_b200.envs import CartPoleEnv, PendulumEnv, PointEnv
     cls = dict(pendulum=PendulumEnv, point=PointEnv, cartpole=CartPoleEnv)[env_name]
-    if hidden == (128, 128):
-        pytest.skip('the device sampler is built for hidden 32 / 64; hidden 128 is covered on host batches below')
     kw = dict(seed_np=5, shuffle='numpy') if env_name == 'cartpole' else {}
     pf, vf_, sf, lf = _run(cls, 'ppo', 'fused', 64, 2, mb, hidden=hidden, **kw)
     ps, vs, ss, ls = _run(cls, 'ppo', 'stepwise', 64, 2, mb, hidden=hidden, **kw)
