@@ -56,6 +56,8 @@ SIGNATURES = {
     'b2g_discount_cumsum_f64': (c_int, [P, c_double, P, c_int64, c_int, P]),
     'b2g_moments_ws_bytes': (c_int64, []),
     'b2g_moments': (c_int, [P, c_int64, P, P, P]),
+    'b2g_moments_static_max_n': (c_int64, []),
+    'b2g_moments_static': (c_int, [P, c_int64, P, P]),
     'b2g_gridworld_step': (c_int, [P, c_int, c_int, c_int, P, P, P, P, P, P, P, c_int64, P]),
     'b2g_gridworld_rollout': (c_int, [P, c_int, c_int, c_int, c_int, P, P, P, c_int, c_int64, P, P, P, P, P, P, P]),
     'b2g_episode_stats': (c_int, [P, c_int, P, P, P, P, c_int64, c_double, c_int64, P, P, P]),

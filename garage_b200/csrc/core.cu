@@ -134,6 +134,53 @@ extern "C" int b2g_moments(const float* x, int64_t n, double* out3, void* ws, vo
     return B2G_OK;
 }
 
+// ---- b2g_moments_static: the same two kernels with the scratch in a file-scope device array, for
+// callers that may not allocate (CUDA graph capture, serving loops).  No counterpart in the reference.
+// Every call on a device shares the array: calls that overlap on the GPU (different streams) race.
+static __device__ __align__(256) double g_moments_scratch[2 * MOM_BLOCKS + 2];
+static const int64_t MOMENTS_STATIC_MAX_N = (int64_t)1 << 28;
+static const int MOMENTS_MAX_DEVICES = 64;
+
+extern "C" int64_t b2g_moments_static_max_n(void) { return MOMENTS_STATIC_MAX_N; }
+
+// device address of the array on the CURRENT device, resolved once per device (the symbol's name in
+// host code is a host-side stand-in, not a device pointer)
+static int moments_scratch_ptr(double** out) {
+    static double* ptrs[MOMENTS_MAX_DEVICES] = {};
+    int dev = -1;
+    B2G_CUDA(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= MOMENTS_MAX_DEVICES) {
+        b2g_set_error("b2g_moments_static: device ordinal %d outside [0, %d)", dev, MOMENTS_MAX_DEVICES);
+        return B2G_ERR_INVALID;
+    }
+    double* p = __atomic_load_n(&ptrs[dev], __ATOMIC_ACQUIRE);
+    if (!p) {
+        B2G_CUDA(cudaGetSymbolAddress((void**)&p, g_moments_scratch));
+        __atomic_store_n(&ptrs[dev], p, __ATOMIC_RELEASE);
+    }
+    *out = p;
+    return B2G_OK;
+}
+
+extern "C" int b2g_moments_static(const float* x, int64_t n, double* out3, void* stream) {
+    B2G_CHECK_ARG(n > 0 && x && out3, "empty input or NULL pointer");
+    if (n > MOMENTS_STATIC_MAX_N) {
+        b2g_set_error("b2g_moments_static: n = %lld exceeds the built-in limit of %lld elements (use b2g_moments "
+                      "with a caller-owned workspace)", (long long)n, (long long)MOMENTS_STATIC_MAX_N);
+        return B2G_ERR_INVALID;
+    }
+    double* w = nullptr;
+    const int rc = moments_scratch_ptr(&w);
+    if (rc != B2G_OK) return rc;
+    cudaStream_t s = (cudaStream_t)stream;
+    // the arrival counter must start at zero; the per-block slots are fully rewritten by every launch
+    B2G_CUDA(cudaMemsetAsync(w + 2 * MOM_BLOCKS, 0, sizeof(double), s));
+    moments_kernel<0><<<MOM_BLOCKS, MOM_THREADS, 0, s>>>(x, n, out3, w);
+    moments_kernel<1><<<MOM_BLOCKS, MOM_THREADS, 0, s>>>(x, n, out3, w);
+    B2G_CHECK_LAUNCH();
+    return B2G_OK;
+}
+
 __global__ void __launch_bounds__(256)
 normalize_adv_kernel(const float* __restrict__ x, const double* __restrict__ st, int center,
                      int positive, float* __restrict__ y, int64_t n) {

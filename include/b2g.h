@@ -90,6 +90,18 @@ int b2g_discount_cumsum_f64(const double* x, double gamma, double* out, int64_t 
 int64_t b2g_moments_ws_bytes(void);
 int b2g_moments(const float* x, int64_t n, double* out3, void* ws, void* stream);
 
+/* b2g_moments_static: b2g_moments without a workspace argument and without any allocation.  It has
+ * no counterpart in the reference; it was added for callers
+ * that cannot allocate device memory (code under CUDA graph capture, tight serving loops, harnesses
+ * that forbid cudaMalloc).  The scratch (594 doubles, 4,752 bytes) is a file-scope __device__ array
+ * that every GPU loading the library holds until exit; its device address is resolved once per
+ * device with cudaGetSymbolAddress.  Same kernels, same results as b2g_moments (bit-identical).
+ * Limit: n <= b2g_moments_static_max_n() = 2^28 elements; larger n returns B2G_ERR_INVALID with a
+ * message.  All calls on one device share the array: calls that overlap on the GPU (two streams)
+ * race; serialise them or use b2g_moments with separate workspaces. */
+int64_t b2g_moments_static_max_n(void);
+int b2g_moments_static(const float* x, int64_t n, double* out3, void* stream);
+
 /* y = (x - mean) / (var + 1e-8) [- min'] : vpg.py:371-377, in place allowed.
  * stats3 = device pointer written by b2g_moments.  positive_adv subtracts the
  * minimum of the centred values (== (min - mean)/(var+eps)). */
