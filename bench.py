@@ -324,9 +324,9 @@ def warm(fn, n, at_least=30):
 
 def ncu_traffic(kernel, **shape):
     """dram bytes per launch of `kernel` from the committed `ncu --set full` capture
-    (profiles/r1_ncu_traffic.json) when it was taken on this exact shape, else None."""
+    (profiles/r2_ncu_traffic.json) when it was taken on this exact shape, else None."""
     try:
-        with open(os.path.join(os.path.dirname(os.path.abspath(__file__)), 'profiles', 'r1_ncu_traffic.json')) as fh:
+        with open(os.path.join(os.path.dirname(os.path.abspath(__file__)), 'profiles', 'r2_ncu_traffic.json')) as fh:
             rec = json.load(fh)[kernel]
     except (OSError, KeyError, ValueError):
         return None
@@ -378,15 +378,16 @@ def kernel_rooflines(a, algo, device):
         ach = flops / (ms * 1e-3) / 1e12
         mlp = dict(bound='tensor', achieved=ach, peak=tf, unit='TFLOP/s', frac=ach / tf,
                    traffic=ncu_traffic('train_loop_kernel', rows=B, minibatch=mb, epochs=a.epochs),
-                   traffic_unit='dram bytes per launch (ncu --set full, profiles/r1_ncu_traffic.json); the '
+                   traffic_unit='dram bytes per launch (ncu --set full, profiles/r2_ncu_traffic.json); the '
                                 'gathered batch (rows x 40 B per epoch) is L2-resident',
                    kernel='train_loop_kernel<O={},A={}> (tcgen05 kind::tf32, 3xTF32 split: the tensor pipe '
                           'executes 3x the algorithmic FLOPs)'.format(O_, A),
                    us_per_launch=ms * 1e3, minibatch_steps_per_launch=steps, us_per_minibatch_step=ms * 1e3 / steps,
                    rows_per_launch=2 * B * a.epochs, peak_kind=kind + ' bf16 sustained',
                    note='algorithmic FLOPs = 3 x 2 x (O*H + H*H + H*A) per row and pass, both networks; '
-                        'K = 64 contractions issued as M64/128 x N64..160 x K8 MMAs whose ~55-65 cycle '
-                        'instruction floor (tools/ld_probe micro-benchmark), not the FLOP rate, bounds them')
+                        'K = 64 contractions issued as M64 x N<=72 x K8 MMAs: 46 cycles per instruction from one '
+                        'issuing thread, 32 cycles of tensor pipe each when both CTAs of an SM issue '
+                        '(tools/ld_probe.cu, profiles/r2_ld_probe.log): instruction latency, not the FLOP rate, bounds them')
     else:
         idx = ops.permutation(B, 0, device=device)
         reps = 50
@@ -422,7 +423,7 @@ def kernel_rooflines(a, algo, device):
     gbs = 17.0 * T * N / (gms * 1e-3) / 1e9
     gae = dict(bound='hbm', achieved=gbs, peak=hbm, unit='GB/s', frac=gbs / hbm,
                traffic=ncu_traffic('gae_time_major_kernel', T=T, N=N), algorithmic_bytes=17.0 * T * N,
-               traffic_unit='dram bytes per launch (ncu --set full, profiles/r1_ncu_traffic.json)',
+               traffic_unit='dram bytes per launch (ncu --set full, profiles/r2_ncu_traffic.json)',
                kernel='gae_time_major_kernel', T=T, N=N, us_per_launch=gms * 1e3,
                footprint_mb=17.0 * T * N / 1e6, peak_kind=kind,
                note='17 algorithmic B per (t,n): r 4 + V 4 + step_type 1 read, A 4 + R 4 written')

@@ -33,19 +33,21 @@ __device__ __forceinline__ void mma(uint32_t d, uint64_t a, uint64_t b, uint32_t
 
 struct Result { long long issue, total, ld; };
 
-template <bool TF32>
-__global__ void __launch_bounds__(128, 1) probe(int M, int N, int reps, Result* out) {
+template <bool TF32, int NACC>
+__global__ void __launch_bounds__(128, 1) probe(int M, int N, int reps, Result* out, int smem_kb = 160, int cols = 512) {
+    out += 2 * blockIdx.x;
     extern __shared__ __align__(1024) uint8_t smem[];
     __shared__ uint32_t tslot;
     __shared__ __align__(8) uint64_t bar;
     const int tid = threadIdx.x;
-    for (int i = tid; i < 160 * 1024 / 16; i += 128) reinterpret_cast<float4*>(smem)[i] = make_float4(0, 0, 0, 0);
+    for (int i = tid; i < smem_kb * 1024 / 16; i += 128) reinterpret_cast<float4*>(smem)[i] = make_float4(0, 0, 0, 0);
     if (tid == 0) {
         asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(smem_u32(&bar)));
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     if (tid < 32) {
-        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], 512;" ::"r"(smem_u32(&tslot)) : "memory");
+        if (cols == 512) asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], 512;" ::"r"(smem_u32(&tslot)) : "memory");
+        else asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], 256;" ::"r"(smem_u32(&tslot)) : "memory");
         asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
     }
     asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
@@ -58,7 +60,11 @@ __global__ void __launch_bounds__(128, 1) probe(int M, int N, int reps, Result* 
         const uint32_t id = idesc(M, N, TF32 ? 2 : 1);
         const uint64_t da = umma_desc(sb, 1024, 512), db = umma_desc(sb + 64 * 1024, 1024, 512);
         t0 = clock64();
-        for (int i = 0; i < reps; ++i) mma<TF32>(tmem, da, db, id, i != 0);
+        // nacc > 1: consecutive instructions accumulate into different TMEM column blocks (independent chains)
+        for (int i = 0; i < reps; i += NACC) {
+#pragma unroll
+            for (int q = 0; q < NACC; ++q) mma<TF32>(tmem + (uint32_t)(q * N), da, db, id, i != 0);
+        }
         t1 = clock64();
         asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(&bar)) : "memory");
         uint32_t done = 0;
@@ -85,17 +91,21 @@ __global__ void __launch_bounds__(128, 1) probe(int M, int N, int reps, Result* 
     if (tid == 0) { out->issue = t1 - t0; out->total = t2 - t0; out->ld = l1 - l0; }
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
     __syncthreads();
-    if (tid < 32) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, 512;" ::"r"(tmem) : "memory");
+    if (tid < 32) {
+        if (cols == 512) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, 512;" ::"r"(tmem) : "memory");
+        else asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, 256;" ::"r"(tmem) : "memory");
+    }
 }
 
-template <bool TF32>
+template <bool TF32, int NACC = 1>
 static void run(int M, int N, int reps) {
+    const int nacc = NACC;
     Result* d;
     cudaMalloc(&d, 2 * sizeof(Result));
     cudaMemset(d, 0, 2 * sizeof(Result));
-    cudaFuncSetAttribute(probe<TF32>, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024);
-    probe<TF32><<<1, 128, 160 * 1024>>>(M, N, reps, d);
-    probe<TF32><<<1, 128, 160 * 1024>>>(M, N, reps, d);
+    cudaFuncSetAttribute(probe<TF32, NACC>, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024);
+    probe<TF32, NACC><<<1, 128, 160 * 1024>>>(M, N, reps, d);
+    probe<TF32, NACC><<<1, 128, 160 * 1024>>>(M, N, reps, d);
     Result r{};
     const cudaError_t e = cudaDeviceSynchronize();
     cudaMemcpy(&r, d, sizeof(r), cudaMemcpyDeviceToHost);
@@ -103,13 +113,47 @@ static void run(int M, int N, int reps) {
     if (e != cudaSuccess) { printf("kind %s M%d N%d: %s\n", TF32 ? "tf32" : "bf16", M, N, cudaGetErrorString(e)); exit(1); }
     const int K = TF32 ? 8 : 16;
     const double cyc = (double)r.total / reps;
-    printf("kind %-4s M%-3d N%-3d K%-2d x %4d: %7.1f cycles / instruction (issue loop %6.1f), %7.1f MAC / cycle; tcgen05.ld 32x32b.x16 + wait %lld cycles\n",
-           TF32 ? "tf32" : "bf16", M, N, K, reps, cyc, (double)r.issue / reps, (double)M * N * K / cyc, r.ld);
+    printf("kind %-4s M%-3d N%-3d K%-2d x %4d acc %d: %7.1f cycles / instruction (issue loop %6.1f), %7.1f MAC / cycle; tcgen05.ld 32x32b.x16 + wait %lld cycles\n",
+           TF32 ? "tf32" : "bf16", M, N, K, reps, nacc, cyc, (double)r.issue / reps, (double)M * N * K / cyc, r.ld);
+}
+
+// two CTAs per SM (80 KB shared memory, 256 TMEM columns each, grid = 2 x SMs), each issuing its own chain: does the
+// per-instruction cost of one CTA change when the other CTA of the SM issues at the same time?
+template <bool TF32>
+static void run_pair(int M, int N, int reps, int per_sm) {
+    int sms = 0;
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, 0);
+    const int grid = per_sm * sms;
+    Result* d;
+    cudaMalloc(&d, 2 * grid * sizeof(Result));
+    cudaMemset(d, 0, 2 * grid * sizeof(Result));
+    cudaFuncSetAttribute(probe<TF32, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024);
+    for (int k = 0; k < 2; ++k) probe<TF32, 1><<<grid, 128, 80 * 1024>>>(M, N, reps, d, 80, 256);
+    const cudaError_t e = cudaDeviceSynchronize();
+    Result* h = (Result*)malloc(2 * grid * sizeof(Result));
+    cudaMemcpy(h, d, 2 * grid * sizeof(Result), cudaMemcpyDeviceToHost);
+    cudaFree(d);
+    if (e != cudaSuccess) { printf("pair M%d N%d: %s\n", M, N, cudaGetErrorString(e)); exit(1); }
+    double sum = 0, mx = 0;
+    for (int b = 0; b < grid; ++b) { const double c = (double)h[2 * b].total / reps; sum += c; if (c > mx) mx = c; }
+    free(h);
+    printf("kind %-4s M%-3d N%-3d x %4d, %d CTA(s) per SM issuing at once: mean %7.1f max %7.1f cycles / instruction per CTA\n",
+           TF32 ? "tf32" : "bf16", M, N, reps, per_sm, sum / grid, mx);
 }
 
 int main() {
     const int shapes[][2] = {{64, 32}, {64, 64}, {64, 128}, {128, 16}, {128, 64}, {128, 128}, {128, 144}, {128, 160}, {128, 256}};
     for (auto& s : shapes) run<true>(s[0], s[1], 256);
     for (auto& s : shapes) run<false>(s[0], s[1], 256);
+    // independent accumulators: is the ~47-cycle floor a dependent-accumulate latency or an issue cost?
+    run<true, 2>(64, 64, 256); run<true, 2>(128, 64, 256); run<true, 2>(64, 16, 256); run<true, 2>(128, 128, 256);
+    run<true, 3>(64, 64, 252); run<true, 3>(128, 64, 252); run<true, 3>(64, 16, 252); run<true, 3>(128, 128, 252);
+    run<true, 4>(64, 64, 256); run<true, 4>(128, 64, 256); run<true, 4>(64, 16, 256); run<true, 4>(128, 128, 256);
+    for (int per_sm : {1, 2}) {
+        run_pair<true>(64, 64, 2048, per_sm);
+        run_pair<true>(64, 16, 2048, per_sm);
+        run_pair<true>(128, 64, 2048, per_sm);
+        run_pair<true>(128, 128, 2048, per_sm);
+    }
     return 0;
 }
