@@ -57,11 +57,15 @@ __device__ unsigned long long g_peer_timeout_ns = 120ull * 1000000000ull;
 // The receive area is double-buffered on the step parity: a slot of step s is rewritten at step
 // s+2, which its writer can only reach after the reader's whole network passed the barrier of step
 // s+1, i.e. after the reader consumed step s.
-__device__ __forceinline__ float slice_allreduce(const NetLoop& n, bool own, int pidx, float tot, unsigned int seq) {
-    if (!own) return 0.0f;
+// Two halves, so that work which does not depend on the peers (the row ids and the gather of the next
+// minibatch) runs while the stores cross NVLink.
+__device__ __forceinline__ void slice_send(const NetLoop& n, int pidx, float tot, unsigned int seq) {
     const int par = (int)(seq & 1u);
     for (int r = 0; r < n.world; ++r)
         if (r != n.rank) st_slot(n.peer_recv[r] + ((size_t)(n.rank * 2 + par) * COMM_P + pidx), tot, seq);
+}
+__device__ __forceinline__ float slice_recv(const NetLoop& n, int pidx, float tot, unsigned int seq) {
+    const int par = (int)(seq & 1u);
     float v[B2G_MAX_RANKS];
     unsigned int missing = 0;
 #pragma unroll
@@ -171,10 +175,11 @@ __device__ __forceinline__ void net_loop(const NetLoop& n, int j, int ctas, uint
             LOOP_STAMP(2);
             net_barrier_arrive(n.sync);
         }
-        if (gstep + 1 < total) {  // rows of the next minibatch: independent of the update, gathered while the
-            set_next_step(a);     // other CTAs finish their tiles
+        const bool more = gstep + 1 < total;
+        if (more) {  // rows of the next minibatch: independent of the update, gathered while the other CTAs
+            set_next_step(a);  // finish their tiles (one GPU) or while the slice sums cross NVLink (several)
             LOOP_STAMP(8);
-            cta.prime(a, j, ctas);
+            if (n.world <= 1 || !live) cta.prime(a, j, ctas);  // (the prologue primes the first minibatch either way)
         }
         LOOP_STAMP(9);
         if (live) {
@@ -202,12 +207,16 @@ __device__ __forceinline__ void net_loop(const NetLoop& n, int j, int ctas, uint
             for (int i = 0; i < MAXB; ++i) sum += pv[i];
             scr[sl * 32 + px] = sum;
             __syncthreads();
+            float tot = 0.0f;
             if (sl == 0 && own) {
-                float tot = 0.0f;
 #pragma unroll
                 for (int k = 0; k < 8; ++k) tot += scr[k * 32 + px];
-                if (n.world > 1) tot = slice_allreduce(n, own, pidx, tot, seq_base + (unsigned int)gstep + 1u);
-                if (own) {
+                if (n.world > 1) slice_send(n, pidx, tot, seq_base + (unsigned int)gstep + 1u);
+            }
+            if (n.world > 1 && more) cta.prime(a, j, ctas);
+            if (sl == 0 && own) {
+                if (n.world > 1) tot = slice_recv(n, pidx, tot, seq_base + (unsigned int)gstep + 1u);
+                {
                     const float* adam_c = reinterpret_cast<const float*>(smem + OFF_SMALL) + Small<O, A>::END;
                     const float g = tot * inv_mb;
                     const float step_size = adam_c[0], bc2_sqrt = adam_c[1];
