@@ -496,7 +496,24 @@ struct Cta {
             // The previous tile's GEMM3 (the last reader of the h1 panels) was waited for in its EPI2; only
             // its GEMM4 may still run, and that reads the DZ and aug panels: the h1 stores go first.
             store_h1(hreg);
+            if (tiles_done > 0) mbar_wait(bar4, par ^ 1);  // every MMA of the previous tile has drained
             stamp(2 + 10 * it);
+            if (tid < R) {
+                const float4 xv = *reinterpret_cast<const float4*>(sX + tid * 4);
+                const float xs[4] = {xv.x, xv.y, xv.z, xv.w};
+                float xh[8], xl[8];
+#pragma unroll
+                for (int i = 0; i < 8; ++i) { xh[i] = 0.0f; xl[i] = 0.0f; }
+                xh[0] = 1.0f;
+#pragma unroll
+                for (int o = 0; o < O; ++o) split_tf32(xs[o], xh[1 + o], xl[1 + o]);
+                uint8_t* aug = smem + OFF_ACT + 2 * PANEL;
+                const uint32_t o0 = chunk_off(tid, 0), o1 = chunk_off(tid, 2);
+                *reinterpret_cast<float4*>(aug + o0) = make_float4(xh[0], xh[1], xh[2], xh[3]);
+                *reinterpret_cast<float4*>(aug + o0 + 16) = make_float4(xh[4], xh[5], xh[6], xh[7]);
+                *reinterpret_cast<float4*>(aug + o1) = make_float4(xl[0], xl[1], xl[2], xl[3]);
+                *reinterpret_cast<float4*>(aug + o1 + 16) = make_float4(xl[4], xl[5], xl[6], xl[7]);
+            }
             stamp(4 + 10 * it);
             fence_async_smem();
             __syncthreads();
@@ -509,28 +526,6 @@ struct Cta {
                 __syncwarp();
             }
             stamp(5 + 10 * it);
-            // GEMM1 reads the h1 panels only; the aug panel (read by GEMM3 / GEMM4) is written while GEMM1 runs,
-            // once the previous tile's GEMM4 has drained -- by warps 4 and 5 (warp 0 is issuing): rows i of sX
-            // are read by thread 2R + i here and rewritten by thread i in publish_rows() at the end of EPI1,
-            // after the pair barrier that joins exactly those two warps
-            if (tiles_done > 0) mbar_wait(bar4, par ^ 1);  // every MMA of the previous tile has drained
-            if (tid >= 2 * R && tid < 3 * R) {
-                const int tr = tid - 2 * R;
-                const float4 xv = *reinterpret_cast<const float4*>(sX + tr * 4);
-                const float xs[4] = {xv.x, xv.y, xv.z, xv.w};
-                float xh[8], xl[8];
-#pragma unroll
-                for (int i = 0; i < 8; ++i) { xh[i] = 0.0f; xl[i] = 0.0f; }
-                xh[0] = 1.0f;
-#pragma unroll
-                for (int o = 0; o < O; ++o) split_tf32(xs[o], xh[1 + o], xl[1 + o]);
-                uint8_t* aug = smem + OFF_ACT + 2 * PANEL;
-                const uint32_t o0 = chunk_off(tr, 0), o1 = chunk_off(tr, 2);
-                *reinterpret_cast<float4*>(aug + o0) = make_float4(xh[0], xh[1], xh[2], xh[3]);
-                *reinterpret_cast<float4*>(aug + o0 + 16) = make_float4(xh[4], xh[5], xh[6], xh[7]);
-                *reinterpret_cast<float4*>(aug + o1) = make_float4(xl[0], xl[1], xl[2], xl[3]);
-                *reinterpret_cast<float4*>(aug + o1 + 16) = make_float4(xl[4], xl[5], xl[6], xl[7]);
-            }
             // Row ids of the tile after next, off the critical path.  Warps 4 and 5 write them, warps 0
             // and 1 read them in publish_rows() at the end of EPI1: the only barrier in between is the
             // pair barrier of EPI1, which joins exactly warps (0, 4) and (1, 5) -- entry i is written by
