@@ -335,6 +335,24 @@ def ncu_traffic(kernel, **shape):
     return rec['dram_read_bytes'] + rec['dram_write_bytes']
 
 
+def smem_pipe(kernel, **shape):
+    """Shared-memory data-pipe utilisation of `kernel` from the committed ncu capture (same shape only):
+    MMA operand fetch + LDS/STS wavefronts as a fraction of the pipe's peak over the whole launch."""
+    try:
+        with open(os.path.join(os.path.dirname(os.path.abspath(__file__)), 'profiles', 'r2_ncu_traffic.json')) as fh:
+            rec = json.load(fh)[kernel]
+    except (OSError, KeyError, ValueError):
+        return None
+    if any(rec.get(k) != v for k, v in shape.items()) or 'smem_tc_pct_of_peak' not in rec:
+        return None
+    return dict(source='ncu --set full, profiles/r2_ncu_traffic.json (not measured live)',
+                mma_operand_fetch_frac=rec['smem_tc_pct_of_peak'] / 100.0,
+                lds_sts_frac=rec['smem_lsu_pct_of_peak'] / 100.0,
+                frac=(rec['smem_tc_pct_of_peak'] + rec['smem_lsu_pct_of_peak']) / 100.0,
+                note='fraction of the l1tex shared-memory data pipe over the whole launch; the tile phases '
+                     '(58 % of a CTA\'s time) carry almost all of it')
+
+
 def kernel_rooflines(a, algo, device):
     """Dominant kernel (the fused training loop: every minibatch step of both networks in one
     launch; falls back to the one-minibatch kernel when the loop does not apply) and the GAE
@@ -387,7 +405,9 @@ def kernel_rooflines(a, algo, device):
                    note='algorithmic FLOPs = 3 x 2 x (O*H + H*H + H*A) per row and pass, both networks; '
                         'K = 64 contractions issued as M64 x N<=72 x K8 MMAs: 46 cycles per instruction from one '
                         'issuing thread, 32 cycles of tensor pipe each when both CTAs of an SM issue '
-                        '(tools/ld_probe.cu, profiles/r2_ld_probe.log): instruction latency, not the FLOP rate, bounds them')
+                        '(tools/ld_probe.cu, profiles/r2_ld_probe.log) = their 4 KB of shared-memory operands at 128 B per '
+                        'cycle. The unit that is full is the shared-memory data pipe (see shared_memory_pipe), not the FLOP rate',
+                   shared_memory_pipe=smem_pipe('train_loop_kernel', rows=B, minibatch=mb, epochs=a.epochs))
     else:
         idx = ops.permutation(B, 0, device=device)
         reps = 50
