@@ -61,8 +61,11 @@ class GPUSampler(Sampler):
     environment copies is `n_envs` if given, else `n_workers * worker_args['n_envs']`.
 
     Args:
-        agents (GaussianMLPPolicy): the policy (its flat CUDA parameter vector is used).
-        envs (BatchedEnv): environment description (PointEnv / PendulumEnv / CartPoleEnv).
+        agents (GaussianMLPPolicy or list): the policy (its flat CUDA parameter vector is used); a list
+            (one per worker, length `n_workers`) gives every worker its own, as in the reference.
+        envs (BatchedEnv or list): environment description (PointEnv / PendulumEnv / CartPoleEnv); a list
+            gives every worker its own (multi-task sampling): each worker is then a group of
+            `worker_args['n_envs']` device envs and `obtain_samples` visits the groups round-robin.
         max_episode_length (int): required, like the reference (local_sampler.py:63-65).
         n_envs (int): environment copies on this rank.
         seed (int): Philox key (defaults to `deterministic.get_seed()` or 0).
@@ -81,14 +84,33 @@ class GPUSampler(Sampler):
                             'max_episode_length)')
         if is_tf_worker:
             raise NotImplementedError('TF workers are out of scope of garage_b200')
-        if isinstance(agents, (list, tuple)) or isinstance(envs, (list, tuple)):
-            raise NotImplementedError('GPUSampler takes one policy and one env description; the env '
-                                      'copies are made on the device')
+        self._groups = None
+        if isinstance(agents, list) or isinstance(envs, list):
+            # one agent / env PER WORKER (local_sampler.py:50-86, worker_factory.py:68-95)
+            lists = [x for x in (agents, envs) if isinstance(x, list)]
+            if n_workers is None:
+                n_workers = len(lists[0])
+            agents_l, envs_l = self._per_worker(agents, n_workers), self._per_worker(envs, n_workers)
+            if all(x is agents_l[0] for x in agents_l) and all(x is envs_l[0] for x in envs_l):
+                agents, envs = agents_l[0], envs_l[0]  # the same objects everywhere: one vectorised worker
+            else:
+                if n_envs is not None and n_envs % n_workers:
+                    raise ValueError('n_envs must be a multiple of n_workers when agents / envs are lists')
+                per = n_envs // n_workers if n_envs is not None else (worker_args or {}).get(
+                    'n_envs', VecWorker.DEFAULT_N_ENVS)
+                self._groups = [
+                    GPUSampler(ag, en, max_episode_length=max_episode_length, seed=seed, n_envs=per,
+                               env_id_offset=int(env_id_offset) + i * per, keep_agent_infos=keep_agent_infos,
+                               deterministic=deterministic)
+                    for i, (ag, en) in enumerate(zip(agents_l, envs_l))]
+                n_envs = per * n_workers
+                agents, envs = agents_l[0], envs_l[0]
         if n_envs is None:
             per = (worker_args or {}).get('n_envs', VecWorker.DEFAULT_N_ENVS)
             n_envs = per * (n_workers if n_workers is not None else psutil.cpu_count(logical=False))
         if n_envs <= 0:
             raise ValueError('n_envs must be positive')
+        self._n_workers = n_workers
         self._policy = agents
         self._env = envs
         self._max_episode_length = max_episode_length
@@ -105,6 +127,16 @@ class GPUSampler(Sampler):
         self._static_pack = None  # (shape key, row statistics, row map) of a never-terminating env
         self._buf = None
         self.total_env_steps = 0
+
+    @staticmethod
+    def _per_worker(objs, n_workers):
+        """`WorkerFactory.prepare_worker_messages` (worker_factory.py:68-95): a list must have one entry per
+        worker, anything else is given to every worker."""
+        if isinstance(objs, list):
+            if len(objs) != n_workers:
+                raise ValueError('Length of list doesn\'t match number of workers')
+            return list(objs)
+        return [objs] * n_workers
 
     @classmethod
     def from_worker_factory(cls, worker_factory, agents, envs):
@@ -172,6 +204,8 @@ class GPUSampler(Sampler):
     def obtain_samples(self, itr, num_samples, agent_update, env_update=None):
         """Collect at least `num_samples` transitions (reference
         local_sampler.py:134-166).  Returns a DeviceEpisodeBatch."""
+        if self._groups is not None:
+            return self._obtain_grouped(itr, num_samples, agent_update, env_update)
         if getattr(self._env if env_update is None else env_update, 'env_id', None) == 'gridworld':
             return self._obtain_gridworld(num_samples, agent_update, env_update)
         self._update(agent_update, env_update)
@@ -318,6 +352,42 @@ class GPUSampler(Sampler):
         return DeviceEpisodeBatch(env_spec=env.spec, dev=d, n_eps=n_eps, n_steps=n_steps, log_std=0.0,
                                   tm=buf, ep_off=ep_off, t_star=t_star, row_map=row_map)
 
+    def _obtain_grouped(self, itr, num_samples, agent_update, env_update):
+        """Per-worker agents / envs: the reference's loop (local_sampler.py:156-166) visits the workers
+        round-robin, takes whatever episodes one `rollout()` of a worker completes and stops as soon as the
+        total reaches `num_samples`.  A worker never contributes more than `num_samples` steps, so every group
+        collects that many on the device, and the visiting order is replayed on the host over the groups'
+        completion rows (one `VecWorker.rollout()` = the rows up to the next one in which an episode ends).
+        Returns a host `EpisodeBatch` (episode / env infos differ per worker): a compatibility path, not the
+        fast one."""
+        from garage_b200._dtypes import EpisodeBatch
+        n = len(self._groups)
+        a_ups, e_ups = self._per_worker(agent_update, n), self._per_worker(env_update, n)
+        rounds = []
+        for g, au, eu in zip(self._groups, a_ups, e_ups):
+            before = g.total_env_steps
+            b = g.obtain_samples(itr, num_samples, au, eu)
+            g.total_env_steps = before
+            ends = b.dev.ep_end.cpu().numpy()
+            eps = b.to_host().split()
+            per_row = []
+            for e, row in zip(eps, ends):  # completion order: a rollout() is a run of equal rows
+                if not per_row or per_row[-1][0] != row:
+                    per_row.append((row, []))
+                per_row[-1][1].append(e)
+            rounds.append([r[1] for r in per_row])
+        out, total, r = [], 0, 0
+        while True:
+            for g, rr in zip(self._groups, rounds):
+                for e in rr[r]:
+                    out.append(e)
+                    total += int(e.lengths.sum())
+                    g.total_env_steps += int(e.lengths.sum())
+                if total >= num_samples:
+                    self.total_env_steps += total
+                    return EpisodeBatch.concatenate(*out)
+            r += 1
+
     def obtain_exact_episodes(self, n_eps_per_worker, agent_update, env_update=None):
         """Exactly `n_eps_per_worker` whole episodes from EVERY env copy, env-major order (reference
         local_sampler.py:168-200 with one env per worker): every env runs from `reset()` for
@@ -326,6 +396,13 @@ class GPUSampler(Sampler):
         k = int(n_eps_per_worker)
         if k <= 0:
             raise ValueError('n_eps_per_worker must be positive')
+        if self._groups is not None:  # worker-major, like the reference's loop over workers
+            from garage_b200._dtypes import EpisodeBatch
+            n = len(self._groups)
+            parts = [g.obtain_exact_episodes(k, au, eu).to_host() for g, au, eu in
+                     zip(self._groups, self._per_worker(agent_update, n), self._per_worker(env_update, n))]
+            self.total_env_steps += sum(int(p.lengths.sum()) for p in parts)
+            return EpisodeBatch.concatenate(*parts)
         self._update(agent_update, env_update)
         env, N, L = self._env, self._n_envs, self._max_len()
         if L == 0:
@@ -378,6 +455,8 @@ class GPUSampler(Sampler):
 
     def shutdown_worker(self):
         """Nothing to shut down: there are no worker processes."""
+        for g in self._groups or ():
+            g.shutdown_worker()
         self._es = None
         self._buf = None
         self._static_pack = None

@@ -116,3 +116,12 @@ def test_episode_batch_to_list_from_list_round_trip():
     cat = EpisodeBatch.concatenate(*b.split())
     np.testing.assert_array_equal(cat.observations, b.observations)
     np.testing.assert_array_equal(cat.lengths, b.lengths)
+
+
+def test_sampler_list_arguments_need_one_entry_per_worker():
+    """worker_factory.py:68-95: a list of agents / envs must have length n_workers (checked without a GPU)."""
+    from garage_b200.sampler import LocalSampler
+    with pytest.raises(ValueError, match="Length of list doesn't match number of workers"):
+        LocalSampler(agents=object(), envs=[object(), object(), object()], max_episode_length=10, n_workers=2)
+    with pytest.raises(ValueError, match="Length of list doesn't match number of workers"):
+        LocalSampler(agents=[object()], envs=object(), max_episode_length=10, n_workers=2)
