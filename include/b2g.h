@@ -203,7 +203,7 @@ int b2g_env_step(int env_id, const double* params, int max_episode_length, doubl
  * Policy parameter vector (float32, the order of GaussianMLPPolicy.state_dict(),
  * torch/policies/gaussian_mlp_policy.py:53-87 with hidden_sizes=(H,H)):
  *   [ log_std (1) | W1 [H,O] | b1 [H] | W2 [H,H] | b2 [H] | W3 [A,H] | b3 [A] ]
- * b2g_mlp_param_count gives its length.  H in {32, 64}; other sizes return
+ * b2g_mlp_param_count gives its length.  H in {32, 64, 128}; other sizes return
  * B2G_ERR_UNSUPPORTED (never a silent fallback).
  */
 int64_t b2g_mlp_param_count(int obs_dim, int hidden, int out_dim);
@@ -376,8 +376,9 @@ int b2g_get_mlp_path(void);
  * place.  shuffle: 0 = rows in order (minibatch = NULL/full batch), 1 = the permutation
  * b2g_permutation(shuffle_seed, counter = step counter at the start of the epoch) would write,
  * evaluated on the fly, 2 = `idx` holds [epochs][n_rows] int32 row ids (the reference's
- * BatchDataset order).  hidden must be 64 (tcgen05 path); workspace holds at least
- * b2g_mlp_train_loop_ws_floats() floats. */
+ * BatchDataset order).  Shapes: see b2g_mlp_train_loop_kind below (tcgen05 loop for hidden 64 and the built
+ * (obs, out) pairs, general CUDA-core loop for hidden 32 / 64 / 128, obs <= 8, out <= 4; anything else returns
+ * B2G_ERR_UNSUPPORTED); workspace holds at least b2g_mlp_train_loop_ws_floats() floats. */
 typedef struct b2g_train_net {
     int obs_dim, hidden, out_dim;
     float* params;                       /* flat parameter vector, updated in place */
