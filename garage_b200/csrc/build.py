@@ -19,7 +19,7 @@ NVCC = os.environ.get('NVCC', '/usr/local/cuda/bin/nvcc')
 FLAGS = [
     '-gencode', 'arch=compute_100a,code=sm_100a', '-O3', '-lineinfo', '-std=c++17',
     '-Xcompiler', '-fPIC',
-    '--expt-relaxed-constexpr', '-Xptxas', '-v',
+    '--expt-relaxed-constexpr', '-Xptxas', '-v', *os.environ.get('B2G_NVCC_EXTRA', '').split(),
 ]
 # precise math is nvcc's default; fast-math is never enabled (fp32 parity)
 

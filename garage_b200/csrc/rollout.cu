@@ -55,7 +55,10 @@ struct RolloutArgs {
     int32_t* ep_len;     // [T,N] or NULL, episode length, written at TERMINAL/TIMEOUT rows only
 };
 
-constexpr int RO_WARPS = 4;
+#ifndef B2G_RO_WARPS
+#define B2G_RO_WARPS 4
+#endif
+constexpr int RO_WARPS = B2G_RO_WARPS;  // warps per CTA (one warp owns G envs)
 
 template <int ENV, int H, int G, bool NORM, bool WS = false>
 __global__ void __launch_bounds__(RO_WARPS * 32)
